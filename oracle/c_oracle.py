@@ -1,0 +1,71 @@
+"""ctypes shim over oracle/liboracle.so (CPU ORACLE — test infrastructure, not product code;
+see the header of oracle.c).  Built by `make -C oracle` (also done by __graft_entry__.build())."""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import List, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class OracleXfer(ctypes.Structure):
+    _fields_ = [("src", ctypes.c_int32), ("dst", ctypes.c_int32), ("layer", ctypes.c_int32),
+                ("_pad", ctypes.c_int32), ("off", ctypes.c_int64), ("size", ctypes.c_int64),
+                ("total", ctypes.c_int64)]
+
+
+def lib() -> ctypes.CDLL:
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(path):
+            subprocess.check_call(["make", "-C", _HERE, "-s"])
+        _LIB = ctypes.CDLL(path)
+        _LIB.oracle_fill.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_int64, ctypes.c_uint64, ctypes.c_void_p]
+        _LIB.oracle_checksum.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]
+        _LIB.oracle_tcp_run.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(OracleXfer),
+                                        ctypes.c_int, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int,
+                                        ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]
+    return _LIB
+
+
+def fill_bytes(kind: int, layer_id: int, size: int, seed: int = 0) -> np.ndarray:
+    out = np.empty(max(size, 0), dtype=np.uint8)
+    rc = lib().oracle_fill(kind, layer_id, size, seed & ((1 << 64) - 1), out.ctypes.data)
+    if rc != 0:
+        raise ValueError("oracle_fill failed")
+    return out
+
+
+def checksum(data: np.ndarray, chunk_bytes: int = 256 * 1024) -> np.ndarray:
+    data = np.ascontiguousarray(data, dtype=np.uint8)
+    n_chunks = (data.size + chunk_bytes - 1) // chunk_bytes
+    out = np.zeros((n_chunks, 2), dtype=np.uint64)
+    rc = lib().oracle_checksum(data.ctypes.data, data.size, chunk_bytes, out.ctypes.data)
+    if rc != 0:
+        raise ValueError("oracle_checksum failed")
+    return out
+
+
+def tcp_run(n_nodes: int, leader: int, xfers: Sequence, src_layers: Sequence[np.ndarray],
+            base_port: int = 18080, verify: bool = True):
+    """Run the transfer list once over loopback TCP.  `src_layers[i]` is the WHOLE source layer of
+    transfer i (uint8 array).  Returns (seconds, bytes_moved)."""
+    n = len(xfers)
+    arr = (OracleXfer * max(n, 1))()
+    ptrs = (ctypes.c_void_p * max(n, 1))()
+    for i, x in enumerate(xfers):
+        arr[i] = OracleXfer(x.src, x.dst, x.layer, 0, x.off, x.size, x.total)
+        ptrs[i] = src_layers[i].ctypes.data
+    sec = ctypes.c_double(0.0)
+    moved = ctypes.c_int64(0)
+    rc = lib().oracle_tcp_run(n_nodes, leader, base_port, arr, n, ptrs, int(verify),
+                              ctypes.byref(sec), ctypes.byref(moved))
+    if rc != 0:
+        raise RuntimeError(f"oracle_tcp_run failed rc={rc}")
+    return sec.value, moved.value
