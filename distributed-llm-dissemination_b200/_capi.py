@@ -1,0 +1,261 @@
+"""ctypes binding of include/dissem.h.  No fallback: a missing libdissem.so raises at load time."""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Iterable, List, Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CHUNK_BYTES = 262144
+FILL_ZERO, FILL_PATTERN, FILL_POISON = 0, 1, 2
+
+_LIB: Optional[ctypes.CDLL] = None
+
+
+class DissemError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"dissem error {code}: {msg}")
+        self.code = code
+
+
+class Xfer(ctypes.Structure):
+    """dissem_xfer: one layerMsg (tempLayerInfo, distributor/transport.go:47-54)."""
+    _fields_ = [("src_node", ctypes.c_int32), ("dst_node", ctypes.c_int32), ("layer", ctypes.c_int32),
+                ("flags", ctypes.c_int32), ("off", ctypes.c_int64), ("size", ctypes.c_int64),
+                ("total", ctypes.c_int64)]
+
+    def __repr__(self):
+        return f"Xfer({self.src_node}->{self.dst_node} L{self.layer} [{self.off},+{self.size})/{self.total})"
+
+
+def lib_path() -> str:
+    return os.path.join(_HERE, "libdissem.so")
+
+
+def load_library() -> ctypes.CDLL:
+    """Load libdissem.so (built in-tree by `make -C distributed-llm-dissemination_b200` or
+    __graft_entry__.build()).  Raises if it is missing — there is no CPU implementation to fall back to."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        raise ImportError(f"{path} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          f"(the engine is CUDA-only; there is no CPU fallback)")
+    L = ctypes.CDLL(path)
+    c = ctypes
+    P = c.c_void_p
+    i64 = c.c_int64
+    sig = {
+        "dissem_version": (c.c_int, []),
+        "dissem_last_error": (c.c_char_p, []),
+        "dissem_device_count": (c.c_int, []),
+        "dissem_init": (c.c_int, [c.c_int, c.POINTER(c.c_int), c.POINTER(P)]),
+        "dissem_close": (c.c_int, [P]),
+        "dissem_n_nodes": (c.c_int, [P]),
+        "dissem_layer_alloc": (c.c_int, [P, c.c_int, c.c_int, i64]),
+        "dissem_layer_free": (c.c_int, [P, c.c_int, c.c_int]),
+        "dissem_layer_info": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(i64), c.POINTER(P)]),
+        "dissem_layer_fill": (c.c_int, [P, c.c_int, c.c_int, c.c_int, c.c_uint64]),
+        "dissem_layer_reset": (c.c_int, [P, c.c_int, c.c_int]),
+        "dissem_layer_write": (c.c_int, [P, c.c_int, c.c_int, P, i64, i64]),
+        "dissem_layer_read": (c.c_int, [P, c.c_int, c.c_int, P, i64, i64]),
+        "dissem_host_alloc": (c.c_int, [c.POINTER(P), i64]),
+        "dissem_host_free": (c.c_int, [P]),
+        "dissem_layer_export": (c.c_int, [P, c.c_int, c.c_int, P]),
+        "dissem_layer_import": (c.c_int, [P, c.c_int, c.c_int, i64, P]),
+        "dissem_send": (c.c_int, [P, c.c_int, c.c_int, c.c_int, i64, i64, i64, c.POINTER(i64)]),
+        "dissem_schedule_submit": (c.c_int, [P, c.POINTER(Xfer), c.c_int, c.POINTER(i64)]),
+        "dissem_schedule_compile": (c.c_int, [P, c.POINTER(Xfer), c.c_int, c.POINTER(i64)]),
+        "dissem_schedule_launch": (c.c_int, [P, i64, c.POINTER(i64)]),
+        "dissem_schedule_free": (c.c_int, [P, i64]),
+        "dissem_schedule_info": (c.c_int, [P, i64, c.POINTER(i64), c.POINTER(c.c_int), c.POINTER(i64)]),
+        "dissem_wait": (c.c_int, [P, i64, c.POINTER(c.c_double)]),
+        "dissem_wait_detail": (c.c_int, [P, i64, c.POINTER(c.c_double), c.POINTER(c.c_double)]),
+        "dissem_poll": (c.c_int, [P, i64, c.POINTER(c.c_int)]),
+        "dissem_layer_checksums": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
+        "dissem_layer_verify": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
+        "dissem_layer_received": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(i64)]),
+        "dissem_set_option": (c.c_int, [P, c.c_char_p, i64]),
+        "dissem_get_option": (c.c_int, [P, c.c_char_p, c.POINTER(i64)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _LIB = L
+    return L
+
+
+def lib() -> ctypes.CDLL:
+    return load_library()
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise DissemError(rc, (lib().dissem_last_error() or b"").decode())
+
+
+def make_xfers(xfers: Iterable) -> "ctypes.Array[Xfer]":
+    """Accepts Xfer structs or any objects/tuples with (src, dst, layer, off, size, total)."""
+    xs = list(xfers)
+    arr = (Xfer * max(len(xs), 1))()
+    for i, x in enumerate(xs):
+        if isinstance(x, Xfer):
+            arr[i] = x
+        elif isinstance(x, (tuple, list)):
+            s, d, l, off, size, total = x
+            arr[i] = Xfer(s, d, l, 0, off, size, total)
+        else:
+            arr[i] = Xfer(x.src, x.dst, x.layer, 0, x.off, x.size, x.total)
+    return arr
+
+
+class Engine:
+    """One dissem_ctx.  `device_of_node[i]` is the CUDA ordinal of node i, or -1 for a node that lives in
+    another process."""
+
+    def __init__(self, device_of_node: Sequence[int]):
+        L = lib()
+        n = len(device_of_node)
+        arr = (ctypes.c_int * n)(*device_of_node)
+        self._ctx = ctypes.c_void_p()
+        _check(L.dissem_init(n, arr, ctypes.byref(self._ctx)))
+        self.n_nodes = n
+        self.device_of_node = list(device_of_node)
+
+    def close(self):
+        if self._ctx:
+            _check(lib().dissem_close(self._ctx))
+            self._ctx = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- store ----
+    def alloc(self, node: int, layer: int, size: int):
+        _check(lib().dissem_layer_alloc(self._ctx, node, layer, size))
+
+    def free(self, node: int, layer: int):
+        _check(lib().dissem_layer_free(self._ctx, node, layer))
+
+    def has(self, node: int, layer: int) -> bool:
+        return lib().dissem_layer_info(self._ctx, node, layer, None, None) == 0
+
+    def info(self, node: int, layer: int):
+        size = ctypes.c_int64()
+        ptr = ctypes.c_void_p()
+        _check(lib().dissem_layer_info(self._ctx, node, layer, ctypes.byref(size), ctypes.byref(ptr)))
+        return size.value, ptr.value
+
+    def fill(self, node: int, layer: int, kind: int, seed: int = 0):
+        _check(lib().dissem_layer_fill(self._ctx, node, layer, kind, seed & ((1 << 64) - 1)))
+
+    def reset(self, node: int, layer: int):
+        _check(lib().dissem_layer_reset(self._ctx, node, layer))
+
+    def write(self, node: int, layer: int, data, off: int = 0, ptr: Optional[int] = None, size: Optional[int] = None):
+        if ptr is None:
+            data = np.ascontiguousarray(data, dtype=np.uint8)
+            ptr, size = data.ctypes.data, data.size
+        _check(lib().dissem_layer_write(self._ctx, node, layer, ptr, off, size))
+
+    def read(self, node: int, layer: int, off: int = 0, size: Optional[int] = None) -> np.ndarray:
+        if size is None:
+            size = self.info(node, layer)[0] - off
+        out = np.empty(size, dtype=np.uint8)
+        _check(lib().dissem_layer_read(self._ctx, node, layer, out.ctypes.data, off, size))
+        return out
+
+    def export(self, node: int, layer: int) -> bytes:
+        buf = (ctypes.c_uint8 * 64)()
+        _check(lib().dissem_layer_export(self._ctx, node, layer, buf))
+        return bytes(buf)
+
+    def import_(self, node: int, layer: int, size: int, handle: bytes):
+        buf = (ctypes.c_uint8 * 64).from_buffer_copy(handle)
+        _check(lib().dissem_layer_import(self._ctx, node, layer, size, buf))
+
+    # ---- transfers ----
+    def send(self, src: int, dst: int, layer: int, off: int, size: int, total: int) -> int:
+        t = ctypes.c_int64()
+        _check(lib().dissem_send(self._ctx, src, dst, layer, off, size, total, ctypes.byref(t)))
+        return t.value
+
+    def submit(self, xfers) -> int:
+        arr = xfers if isinstance(xfers, ctypes.Array) else make_xfers(xfers)
+        n = len(xfers) if not isinstance(xfers, ctypes.Array) else len(arr)
+        t = ctypes.c_int64()
+        _check(lib().dissem_schedule_submit(self._ctx, arr, n, ctypes.byref(t)))
+        return t.value
+
+    def compile(self, xfers) -> int:
+        xs = list(xfers)
+        arr = make_xfers(xs)
+        s = ctypes.c_int64()
+        _check(lib().dissem_schedule_compile(self._ctx, arr, len(xs), ctypes.byref(s)))
+        return s.value
+
+    def launch(self, sched: int) -> int:
+        t = ctypes.c_int64()
+        _check(lib().dissem_schedule_launch(self._ctx, sched, ctypes.byref(t)))
+        return t.value
+
+    def sched_free(self, sched: int):
+        _check(lib().dissem_schedule_free(self._ctx, sched))
+
+    def sched_info(self, sched: int):
+        units, launches, nbytes = ctypes.c_int64(), ctypes.c_int(), ctypes.c_int64()
+        _check(lib().dissem_schedule_info(self._ctx, sched, ctypes.byref(units), ctypes.byref(launches),
+                                          ctypes.byref(nbytes)))
+        return units.value, launches.value, nbytes.value
+
+    def wait(self, ticket: int) -> float:
+        ms = ctypes.c_double()
+        _check(lib().dissem_wait(self._ctx, ticket, ctypes.byref(ms)))
+        return ms.value
+
+    def wait_detail(self, ticket: int):
+        """-> (batch ms, copy-kernel ms), both device time from CUDA events on the engine's stream."""
+        ms, cms = ctypes.c_double(), ctypes.c_double()
+        _check(lib().dissem_wait_detail(self._ctx, ticket, ctypes.byref(ms), ctypes.byref(cms)))
+        return ms.value, cms.value
+
+    def poll(self, ticket: int) -> bool:
+        d = ctypes.c_int()
+        _check(lib().dissem_poll(self._ctx, ticket, ctypes.byref(d)))
+        return bool(d.value)
+
+    # ---- verification ----
+    def _n_chunks(self, node, layer):
+        return (self.info(node, layer)[0] + CHUNK_BYTES - 1) // CHUNK_BYTES
+
+    def checksums(self, node: int, layer: int) -> np.ndarray:
+        n = self._n_chunks(node, layer)
+        out = np.zeros((n, 2), dtype=np.uint64)
+        _check(lib().dissem_layer_checksums(self._ctx, node, layer, out.ctypes.data, n))
+        return out
+
+    def verify(self, node: int, layer: int) -> np.ndarray:
+        n = self._n_chunks(node, layer)
+        out = np.zeros((n, 2), dtype=np.uint64)
+        _check(lib().dissem_layer_verify(self._ctx, node, layer, out.ctypes.data, n))
+        return out
+
+    def received(self, node: int, layer: int) -> int:
+        v = ctypes.c_int64()
+        _check(lib().dissem_layer_received(self._ctx, node, layer, ctypes.byref(v)))
+        return v.value
+
+    def set_option(self, key: str, value: int):
+        _check(lib().dissem_set_option(self._ctx, key.encode(), value))
+
+    def get_option(self, key: str) -> int:
+        v = ctypes.c_int64()
+        _check(lib().dissem_get_option(self._ctx, key.encode(), ctypes.byref(v)))
+        return v.value

@@ -1,0 +1,791 @@
+// Host engine behind the C ABI of include/dissem.h: the HBM layer store, the schedule compiler and the
+// launch/wait machinery.  Reference citations are in the header; this file only implements them.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/dissem.h"
+#include "dissem_engine.h"
+#include "dissem_kernels.cuh"
+
+namespace dissem {
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+int set_error(int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+const char *last_error() { return g_err.c_str(); }
+
+#define CUDA_TRY(expr)                                                                                  \
+    do {                                                                                                \
+        cudaError_t _e = (expr);                                                                        \
+        if (_e != cudaSuccess)                                                                          \
+            return set_error(_e == cudaErrorNoDevice || _e == cudaErrorInsufficientDriver ? DISSEM_ENODEV \
+                                                                                          : DISSEM_ECUDA, \
+                             "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// layer buffers
+// ------------------------------------------------------------------------------------------------
+// [ layer bytes | pad to 4 KiB | received counter (256 B slot) | checksum table: 16 B per chunk ]
+static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+int64_t LayerBuf::n_chunks() const { return (size + kChunkBytes - 1) / kChunkBytes; }
+int64_t LayerBuf::trailer_off() const { return align_up(std::max<int64_t>(size, 1), 4096); }
+// rounded to 2 MiB so that every layer owns its pages (an IPC handle exports whole pages)
+int64_t LayerBuf::alloc_bytes() const { return align_up(trailer_off() + 256 + align_up(std::max<int64_t>(n_chunks(), 1) * 16, 256), 2 << 20); }
+unsigned long long *LayerBuf::received() const { return reinterpret_cast<unsigned long long *>(base + trailer_off()); }
+unsigned long long *LayerBuf::csum() const { return reinterpret_cast<unsigned long long *>(base + trailer_off() + 256); }
+int64_t LayerBuf::trailer_bytes() const { return alloc_bytes() - trailer_off(); }
+
+struct DeviceState {
+    int dev = -1;
+    int n_sm = 0;
+    cudaStream_t stream = nullptr;
+    SchedCounters *counters = nullptr;   // kernel scratch: ticket + drained-CTA count
+};
+
+struct SchedPart {
+    int dev_slot = -1;
+    XferDesc *d_descs = nullptr;
+    int n_descs = 0;
+    long long total_units = 0;
+    int64_t bytes = 0;
+};
+
+struct Sched {
+    std::vector<SchedPart> parts;
+    int unit_shift = kChunkShift;
+    int64_t units = 0, bytes = 0;
+};
+
+struct TicketPart {
+    int dev_slot;
+    cudaEvent_t start, mid, end;      // start | zero_csum | mid | copy_csum | end
+};
+struct Ticket {
+    std::vector<TicketPart> parts;
+};
+
+}  // namespace dissem
+
+using namespace dissem;
+
+struct dissem_ctx {
+    std::mutex mu;
+    int n_nodes = 0;
+    std::vector<int> node_dev_slot;                    // node -> index into devs, or -1 (remote)
+    std::vector<std::map<int, LayerBuf>> layers;       // node -> layer -> buffer
+    std::vector<DeviceState> devs;
+    std::map<int64_t, Sched> scheds;
+    std::map<int64_t, Ticket> tickets;
+    int64_t next_id = 1;
+    // options
+    int64_t opt_ctas_per_sm = 0, opt_variant = 0, opt_unit_bytes = 0, opt_reg_cfg = 0;
+};
+
+namespace dissem {
+
+static int check_node(dissem_ctx *ctx, int node) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    if (node < 0 || node >= ctx->n_nodes) return set_error(DISSEM_ENOENT, "node %d out of range [0,%d)", node, ctx->n_nodes);
+    return 0;
+}
+
+static int find_layer(dissem_ctx *ctx, int node, int layer, LayerBuf **out) {
+    int rc = check_node(ctx, node);
+    if (rc) return rc;
+    auto it = ctx->layers[node].find(layer);
+    if (it == ctx->layers[node].end()) return set_error(DISSEM_ENOENT, "node %d holds no layer %d", node, layer);
+    *out = &it->second;
+    return 0;
+}
+
+static int local_dev(dissem_ctx *ctx, int node, DeviceState **out) {
+    int rc = check_node(ctx, node);
+    if (rc) return rc;
+    int slot = ctx->node_dev_slot[node];
+    if (slot < 0) return set_error(DISSEM_EINVAL, "node %d is not local to this process", node);
+    *out = &ctx->devs[slot];
+    return 0;
+}
+
+static void free_sched(dissem_ctx *ctx, Sched &s) {
+    for (auto &p : s.parts) {
+        if (p.d_descs) {
+            cudaSetDevice(ctx->devs[p.dev_slot].dev);
+            cudaFree(p.d_descs);
+        }
+    }
+    s.parts.clear();
+}
+
+static int pick_unit_shift(dissem_ctx *ctx, const std::vector<std::vector<dissem_xfer>> &by_dev) {
+    if (ctx->opt_unit_bytes > 0) {
+        int s = 12;
+        while ((1ll << s) < ctx->opt_unit_bytes) ++s;
+        return std::min(std::max(s, 12), kChunkShift);
+    }
+    // auto: 256 KiB units unless that leaves the persistent grid starved (small layers: the README case)
+    int shift = kChunkShift;
+    for (; shift > 14; --shift) {
+        bool starved = false;
+        for (size_t slot = 0; slot < by_dev.size(); ++slot) {
+            if (by_dev[slot].empty()) continue;
+            long long units = 0;
+            for (auto &x : by_dev[slot]) units += units_of(x.off, x.size, shift);
+            if (units < 4ll * ctx->devs[slot].n_sm) starved = true;
+        }
+        if (!starved) break;
+    }
+    return shift;
+}
+
+static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched *out) {
+    if (n < 0 || (n > 0 && !xfers)) return set_error(DISSEM_EINVAL, "bad transfer list");
+    std::vector<std::vector<dissem_xfer>> by_dev(ctx->devs.size());
+    for (int i = 0; i < n; ++i) {
+        const dissem_xfer &x = xfers[i];
+        int rc = check_node(ctx, x.src_node);
+        if (rc) return rc;
+        rc = check_node(ctx, x.dst_node);
+        if (rc) return rc;
+        if (x.size < 0 || x.off < 0 || x.off + x.size > x.total)
+            return set_error(DISSEM_ERANGE, "transfer %d: [%lld,+%lld) outside layer of %lld bytes", i,
+                             (long long)x.off, (long long)x.size, (long long)x.total);
+        int slot = ctx->node_dev_slot[x.src_node];
+        if (slot < 0) continue;          // the owner process of src_node runs it
+        if (x.size == 0) continue;       // an empty layerMsg moves nothing (LayerSize 0)
+        by_dev[slot].push_back(x);
+    }
+    out->unit_shift = pick_unit_shift(ctx, by_dev);
+    for (size_t slot = 0; slot < by_dev.size(); ++slot) {
+        if (by_dev[slot].empty()) continue;
+        std::vector<XferDesc> descs;
+        long long units = 0;
+        int64_t bytes = 0;
+        for (auto &x : by_dev[slot]) {
+            LayerBuf *src = nullptr, *dst = nullptr;
+            int rc = find_layer(ctx, x.src_node, x.layer, &src);
+            if (rc) return rc;
+            rc = find_layer(ctx, x.dst_node, x.layer, &dst);
+            if (rc) return rc;
+            if (src->size != x.total || dst->size != x.total)
+                return set_error(DISSEM_ERANGE, "layer %d: total %lld but src holds %lld and dst %lld bytes", x.layer,
+                                 (long long)x.total, (long long)src->size, (long long)dst->size);
+            if (src->base == dst->base) return set_error(DISSEM_EINVAL, "layer %d: source and destination are the same buffer", x.layer);
+            XferDesc d;
+            memset(&d, 0, sizeof d);
+            d.src = src->base;
+            d.dst = dst->base;
+            d.csum = dst->csum();
+            d.received = dst->received();
+            d.off = x.off;
+            d.size = x.size;
+            d.total = x.total;
+            d.first_unit = units;
+            d.flags = 0;
+            units += units_of(x.off, x.size, out->unit_shift);
+            bytes += x.size;
+            descs.push_back(d);
+        }
+        SchedPart part;
+        part.dev_slot = (int)slot;
+        part.n_descs = (int)descs.size();
+        part.total_units = units;
+        part.bytes = bytes;
+        CUDA_TRY(cudaSetDevice(ctx->devs[slot].dev));
+        CUDA_TRY(cudaMalloc(&part.d_descs, descs.size() * sizeof(XferDesc)));
+        out->parts.push_back(part);
+        // stream-ordered upload from pageable memory: the copy is staged before the call returns
+        CUDA_TRY(cudaMemcpyAsync(part.d_descs, descs.data(), descs.size() * sizeof(XferDesc), cudaMemcpyHostToDevice,
+                                 ctx->devs[slot].stream));
+        out->units += units;
+        out->bytes += bytes;
+    }
+    return 0;
+}
+
+static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
+    for (auto &p : s.parts) {
+        DeviceState &ds = ctx->devs[p.dev_slot];
+        CUDA_TRY(cudaSetDevice(ds.dev));
+        TicketPart tp;
+        tp.dev_slot = p.dev_slot;
+        CUDA_TRY(cudaEventCreate(&tp.start));
+        CUDA_TRY(cudaEventCreate(&tp.mid));
+        CUDA_TRY(cudaEventCreate(&tp.end));
+        t->parts.push_back(tp);
+        CUDA_TRY(cudaEventRecord(tp.start, ds.stream));
+        CUDA_TRY(launch_zero_csum(p.d_descs, p.n_descs, ds.stream));
+        CUDA_TRY(cudaEventRecord(tp.mid, ds.stream));
+        LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg};
+        CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
+        CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
+    }
+    return 0;
+}
+
+static void drop_ticket(Ticket &t) {
+    for (auto &p : t.parts) {
+        cudaEventDestroy(p.start);
+        cudaEventDestroy(p.mid);
+        cudaEventDestroy(p.end);
+    }
+    t.parts.clear();
+}
+
+}  // namespace dissem
+
+// ====================================================================================================
+// C ABI
+// ====================================================================================================
+extern "C" {
+
+int dissem_version(void) { return DISSEM_VERSION; }
+const char *dissem_last_error(void) { return dissem::last_error(); }
+
+int dissem_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int dissem_init(int n_nodes, const int *device_of_node, dissem_ctx **out) {
+    if (n_nodes <= 0 || !device_of_node || !out) return set_error(DISSEM_EINVAL, "dissem_init: bad arguments");
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        cudaGetLastError();
+        return set_error(DISSEM_ENODEV, "no usable CUDA device (%s); this library has no CPU path",
+                         e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    std::unique_ptr<dissem_ctx> ctx(new dissem_ctx);
+    ctx->n_nodes = n_nodes;
+    ctx->node_dev_slot.assign(n_nodes, -1);
+    ctx->layers.resize(n_nodes);
+    for (int i = 0; i < n_nodes; ++i) {
+        int dev = device_of_node[i];
+        if (dev < 0) continue;
+        if (dev >= n_dev) return set_error(DISSEM_EINVAL, "node %d mapped to device %d but only %d visible", i, dev, n_dev);
+        int slot = -1;
+        for (size_t s = 0; s < ctx->devs.size(); ++s)
+            if (ctx->devs[s].dev == dev) slot = (int)s;
+        if (slot < 0) {
+            DeviceState ds;
+            ds.dev = dev;
+            CUDA_TRY(cudaSetDevice(dev));
+            CUDA_TRY(cudaDeviceGetAttribute(&ds.n_sm, cudaDevAttrMultiProcessorCount, dev));
+            CUDA_TRY(cudaStreamCreateWithFlags(&ds.stream, cudaStreamNonBlocking));
+            CUDA_TRY(cudaMalloc(&ds.counters, sizeof(SchedCounters)));
+            CUDA_TRY(cudaMemset(ds.counters, 0, sizeof(SchedCounters)));
+            ctx->devs.push_back(ds);
+            slot = (int)ctx->devs.size() - 1;
+        }
+        ctx->node_dev_slot[i] = slot;
+    }
+    // peer access between all local devices (single-process multi-GPU)
+    for (auto &a : ctx->devs)
+        for (auto &b : ctx->devs) {
+            if (a.dev == b.dev) continue;
+            int can = 0;
+            CUDA_TRY(cudaDeviceCanAccessPeer(&can, a.dev, b.dev));
+            if (!can) return set_error(DISSEM_ENOTSUP, "device %d cannot access device %d", a.dev, b.dev);
+            CUDA_TRY(cudaSetDevice(a.dev));
+            cudaError_t pe = cudaDeviceEnablePeerAccess(b.dev, 0);
+            if (pe == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (pe != cudaSuccess) return set_error(DISSEM_ECUDA, "cudaDeviceEnablePeerAccess(%d->%d): %s", a.dev, b.dev, cudaGetErrorString(pe));
+        }
+    *out = ctx.release();
+    return DISSEM_OK;
+}
+
+int dissem_close(dissem_ctx *ctx) {
+    if (!ctx) return DISSEM_OK;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        for (auto &ds : ctx->devs) {
+            cudaSetDevice(ds.dev);
+            cudaStreamSynchronize(ds.stream);
+        }
+        for (auto &kv : ctx->tickets) drop_ticket(kv.second);
+        for (auto &kv : ctx->scheds) free_sched(ctx, kv.second);
+        for (int n = 0; n < ctx->n_nodes; ++n)
+            for (auto &kv : ctx->layers[n]) {
+                LayerBuf &lb = kv.second;
+                if (lb.imported) cudaIpcCloseMemHandle(lb.base);
+                else {
+                    cudaSetDevice(lb.device);
+                    cudaFree(lb.base);
+                }
+            }
+        for (auto &ds : ctx->devs) {
+            cudaSetDevice(ds.dev);
+            cudaFree(ds.counters);
+            cudaStreamDestroy(ds.stream);
+        }
+    }
+    delete ctx;
+    return DISSEM_OK;
+}
+
+int dissem_n_nodes(dissem_ctx *ctx) { return ctx ? ctx->n_nodes : set_error(DISSEM_EINVAL, "null context"); }
+
+int dissem_layer_alloc(dissem_ctx *ctx, int node, int layer, int64_t size) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceState *ds = nullptr;
+    int rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    if (size < 0) size = 0;                                   // cmd/config.go:100-102
+    if (ctx->layers[node].count(layer)) return set_error(DISSEM_EEXIST, "node %d already holds layer %d", node, layer);
+    LayerBuf lb;
+    lb.size = size;
+    lb.device = ds->dev;
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, (size_t)lb.alloc_bytes());
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        return set_error(DISSEM_ENOMEM, "out of HBM allocating %lld bytes for layer %d on node %d", (long long)lb.alloc_bytes(), layer, node);
+    }
+    CUDA_TRY(e);
+    lb.base = static_cast<uint8_t *>(p);
+    CUDA_TRY(cudaMemsetAsync(lb.base + lb.trailer_off(), 0, (size_t)lb.trailer_bytes(), ds->stream));
+    ctx->layers[node][layer] = lb;
+    return DISSEM_OK;
+}
+
+int dissem_layer_free(dissem_ctx *ctx, int node, int layer) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    for (auto &ds : ctx->devs) {          // nothing in flight may still touch it
+        CUDA_TRY(cudaSetDevice(ds.dev));
+        CUDA_TRY(cudaStreamSynchronize(ds.stream));
+    }
+    if (lb->imported) CUDA_TRY(cudaIpcCloseMemHandle(lb->base));
+    else {
+        CUDA_TRY(cudaSetDevice(lb->device));
+        CUDA_TRY(cudaFree(lb->base));
+    }
+    ctx->layers[node].erase(layer);
+    return DISSEM_OK;
+}
+
+int dissem_layer_info(dissem_ctx *ctx, int node, int layer, int64_t *size_out, void **device_ptr_out) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    if (size_out) *size_out = lb->size;
+    if (device_ptr_out) *device_ptr_out = lb->base;
+    return DISSEM_OK;
+}
+
+int dissem_layer_fill(dissem_ctx *ctx, int node, int layer, int kind, uint64_t seed) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    if (lb->size == 0) return DISSEM_OK;
+    switch (kind) {
+        case DISSEM_FILL_ZERO: CUDA_TRY(cudaMemsetAsync(lb->base, 0, (size_t)lb->size, ds->stream)); break;
+        case DISSEM_FILL_POISON: CUDA_TRY(cudaMemsetAsync(lb->base, 0xA5, (size_t)lb->size, ds->stream)); break;
+        case DISSEM_FILL_PATTERN:
+            CUDA_TRY(launch_fill_pattern(lb->base, lb->size, (unsigned long long)(unsigned int)layer, seed, ds->n_sm, ds->stream));
+            break;
+        default: return set_error(DISSEM_EINVAL, "unknown fill kind %d", kind);
+    }
+    return DISSEM_OK;
+}
+
+int dissem_layer_reset(dissem_ctx *ctx, int node, int layer) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    CUDA_TRY(cudaMemsetAsync(lb->base + lb->trailer_off(), 0, (size_t)lb->trailer_bytes(), ds->stream));
+    return DISSEM_OK;
+}
+
+int dissem_layer_write(dissem_ctx *ctx, int node, int layer, const void *host, int64_t off, int64_t size) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    if (off < 0 || size < 0 || off + size > lb->size) return set_error(DISSEM_ERANGE, "write [%lld,+%lld) outside layer of %lld bytes", (long long)off, (long long)size, (long long)lb->size);
+    if (size == 0) return DISSEM_OK;
+    if (!host) return set_error(DISSEM_EINVAL, "null host pointer");
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    CUDA_TRY(cudaMemcpyAsync(lb->base + off, host, (size_t)size, cudaMemcpyHostToDevice, ds->stream));
+    return DISSEM_OK;
+}
+
+int dissem_layer_read(dissem_ctx *ctx, int node, int layer, void *host, int64_t off, int64_t size) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    if (off < 0 || size < 0 || off + size > lb->size) return set_error(DISSEM_ERANGE, "read [%lld,+%lld) outside layer of %lld bytes", (long long)off, (long long)size, (long long)lb->size);
+    if (size == 0) return DISSEM_OK;
+    if (!host) return set_error(DISSEM_EINVAL, "null host pointer");
+    for (auto &d : ctx->devs) {           // a peer GPU may still be pushing into this layer
+        CUDA_TRY(cudaSetDevice(d.dev));
+        CUDA_TRY(cudaStreamSynchronize(d.stream));
+    }
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    CUDA_TRY(cudaMemcpyAsync(host, lb->base + off, (size_t)size, cudaMemcpyDeviceToHost, ds->stream));
+    CUDA_TRY(cudaStreamSynchronize(ds->stream));
+    return DISSEM_OK;
+}
+
+int dissem_host_alloc(void **out, int64_t size) {
+    if (!out || size < 0) return set_error(DISSEM_EINVAL, "dissem_host_alloc: bad arguments");
+    CUDA_TRY(cudaHostAlloc(out, (size_t)std::max<int64_t>(size, 1), cudaHostAllocPortable));
+    return DISSEM_OK;
+}
+int dissem_host_free(void *p) {
+    if (!p) return DISSEM_OK;
+    CUDA_TRY(cudaFreeHost(p));
+    return DISSEM_OK;
+}
+
+int dissem_layer_export(dissem_ctx *ctx, int node, int layer, uint8_t handle_out[64]) {
+    if (!ctx || !handle_out) return set_error(DISSEM_EINVAL, "dissem_layer_export: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    if (lb->imported) return set_error(DISSEM_EINVAL, "layer %d of node %d is itself imported", layer, node);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaSetDevice(lb->device));
+    CUDA_TRY(cudaIpcGetMemHandle(&h, lb->base));
+    memcpy(handle_out, &h, 64);
+    return DISSEM_OK;
+}
+
+int dissem_layer_import(dissem_ctx *ctx, int node, int layer, int64_t size, const uint8_t handle[64]) {
+    if (!ctx || !handle) return set_error(DISSEM_EINVAL, "dissem_layer_import: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = check_node(ctx, node);
+    if (rc) return rc;
+    if (ctx->node_dev_slot[node] >= 0) return set_error(DISSEM_EINVAL, "node %d is local; import is for remote nodes", node);
+    if (ctx->layers[node].count(layer)) return set_error(DISSEM_EEXIST, "layer %d of node %d already imported", layer, node);
+    if (ctx->devs.empty()) return set_error(DISSEM_EINVAL, "no local device to map the layer on");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    // Map through the first local device; with peer access enabled by the open, every kernel of this
+    // process that runs there can store into it.
+    CUDA_TRY(cudaSetDevice(ctx->devs[0].dev));
+    void *p = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    LayerBuf lb;
+    lb.size = size < 0 ? 0 : size;
+    lb.base = static_cast<uint8_t *>(p);
+    lb.imported = true;
+    lb.device = -1;
+    ctx->layers[node][layer] = lb;
+    return DISSEM_OK;
+}
+
+int dissem_schedule_compile(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_sched *out) {
+    if (!ctx || !out) return set_error(DISSEM_EINVAL, "dissem_schedule_compile: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Sched s;
+    int rc = compile_sched(ctx, xfers, n, &s);
+    if (rc) {
+        free_sched(ctx, s);
+        return rc;
+    }
+    int64_t id = ctx->next_id++;
+    ctx->scheds[id] = std::move(s);
+    *out = id;
+    return DISSEM_OK;
+}
+
+int dissem_schedule_launch(dissem_ctx *ctx, dissem_sched sched, dissem_ticket *out) {
+    if (!ctx || !out) return set_error(DISSEM_EINVAL, "dissem_schedule_launch: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->scheds.find(sched);
+    if (it == ctx->scheds.end()) return set_error(DISSEM_ENOENT, "unknown schedule %lld", (long long)sched);
+    Ticket t;
+    int rc = launch_sched(ctx, it->second, &t);
+    if (rc) {
+        drop_ticket(t);
+        return rc;
+    }
+    int64_t id = ctx->next_id++;
+    ctx->tickets[id] = std::move(t);
+    *out = id;
+    return DISSEM_OK;
+}
+
+int dissem_schedule_free(dissem_ctx *ctx, dissem_sched sched) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->scheds.find(sched);
+    if (it == ctx->scheds.end()) return set_error(DISSEM_ENOENT, "unknown schedule %lld", (long long)sched);
+    for (auto &p : it->second.parts) {       // the kernels read the descriptor table
+        CUDA_TRY(cudaSetDevice(ctx->devs[p.dev_slot].dev));
+        CUDA_TRY(cudaStreamSynchronize(ctx->devs[p.dev_slot].stream));
+    }
+    free_sched(ctx, it->second);
+    ctx->scheds.erase(it);
+    return DISSEM_OK;
+}
+
+int dissem_schedule_info(dissem_ctx *ctx, dissem_sched sched, int64_t *units_out, int *launches_out, int64_t *bytes_out) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->scheds.find(sched);
+    if (it == ctx->scheds.end()) return set_error(DISSEM_ENOENT, "unknown schedule %lld", (long long)sched);
+    if (units_out) *units_out = it->second.units;
+    if (launches_out) *launches_out = 2 * (int)it->second.parts.size();   // zero_csum + copy_csum per source GPU
+    if (bytes_out) *bytes_out = it->second.bytes;
+    return DISSEM_OK;
+}
+
+int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_ticket *out) {
+    dissem_sched s = 0;
+    int rc = dissem_schedule_compile(ctx, xfers, n, &s);
+    if (rc) return rc;
+    rc = dissem_schedule_launch(ctx, s, out);
+    // the descriptor table must outlive the kernels: free it when the ticket completes
+    if (rc == DISSEM_OK) {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        // keep the schedule id inside the ticket by parking it under the negative ticket key
+        ctx->scheds[-(*out)] = std::move(ctx->scheds[s]);
+        ctx->scheds.erase(s);
+    } else {
+        dissem_schedule_free(ctx, s);
+    }
+    return rc;
+}
+
+int dissem_send(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t off, int64_t size, int64_t total,
+                dissem_ticket *out) {
+    dissem_xfer x;
+    memset(&x, 0, sizeof x);
+    x.src_node = src_node;
+    x.dst_node = dst_node;
+    x.layer = layer;
+    x.off = off;
+    x.size = size;
+    x.total = total;
+    return dissem_schedule_submit(ctx, &x, 1, out);
+}
+
+int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out) { return dissem_wait_detail(ctx, ticket, ms_out, nullptr); }
+
+int dissem_wait_detail(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out, double *copy_ms_out) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    Ticket t;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        auto it = ctx->tickets.find(ticket);
+        if (it == ctx->tickets.end()) return set_error(DISSEM_ENOENT, "unknown ticket %lld", (long long)ticket);
+        t = std::move(it->second);
+        ctx->tickets.erase(it);
+    }
+    // wait outside the lock: other goroutines keep calling Send meanwhile (node.go:343)
+    double ms = 0.0, copy_ms = 0.0;
+    int rc = DISSEM_OK;
+    for (auto &p : t.parts) {
+        cudaError_t e = cudaEventSynchronize(p.end);
+        if (e != cudaSuccess) {
+            rc = set_error(DISSEM_ECUDA, "transfer failed: %s", cudaGetErrorString(e));
+            break;
+        }
+        float f = 0.f;
+        e = cudaEventElapsedTime(&f, p.start, p.end);
+        if (e != cudaSuccess) {
+            rc = set_error(DISSEM_ECUDA, "cudaEventElapsedTime: %s", cudaGetErrorString(e));
+            break;
+        }
+        ms = std::max(ms, (double)f);
+        if (cudaEventElapsedTime(&f, p.mid, p.end) == cudaSuccess) copy_ms = std::max(copy_ms, (double)f);
+    }
+    drop_ticket(t);
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        auto sit = ctx->scheds.find(-ticket);       // schedule parked by dissem_schedule_submit
+        if (sit != ctx->scheds.end()) {
+            free_sched(ctx, sit->second);
+            ctx->scheds.erase(sit);
+        }
+    }
+    if (rc == DISSEM_OK && ms_out) *ms_out = ms;
+    if (rc == DISSEM_OK && copy_ms_out) *copy_ms_out = copy_ms;
+    return rc;
+}
+
+int dissem_poll(dissem_ctx *ctx, dissem_ticket ticket, int *done_out) {
+    if (!ctx || !done_out) return set_error(DISSEM_EINVAL, "dissem_poll: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->tickets.find(ticket);
+    if (it == ctx->tickets.end()) return set_error(DISSEM_ENOENT, "unknown ticket %lld", (long long)ticket);
+    int done = 1;
+    for (auto &p : it->second.parts) {
+        cudaError_t e = cudaEventQuery(p.end);
+        if (e == cudaErrorNotReady) { done = 0; cudaGetLastError(); }
+        else if (e != cudaSuccess) return set_error(DISSEM_ECUDA, "transfer failed: %s", cudaGetErrorString(e));
+    }
+    *done_out = done;
+    return DISSEM_OK;
+}
+
+static int read_trailer(dissem_ctx *ctx, int node, int layer, int64_t byte_off, void *out, int64_t bytes) {
+    LayerBuf *lb = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    for (auto &d : ctx->devs) {
+        CUDA_TRY(cudaSetDevice(d.dev));
+        CUDA_TRY(cudaStreamSynchronize(d.stream));
+    }
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    CUDA_TRY(cudaMemcpyAsync(out, lb->base + lb->trailer_off() + byte_off, (size_t)bytes, cudaMemcpyDeviceToHost, ds->stream));
+    CUDA_TRY(cudaStreamSynchronize(ds->stream));
+    return DISSEM_OK;
+}
+
+int dissem_layer_checksums(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks) {
+    if (!ctx || (!out && n_chunks > 0)) return set_error(DISSEM_EINVAL, "dissem_layer_checksums: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    if (n_chunks != lb->n_chunks()) return set_error(DISSEM_EINVAL, "layer %d has %lld chunks, caller passed %lld", layer, (long long)lb->n_chunks(), (long long)n_chunks);
+    if (n_chunks == 0) return DISSEM_OK;
+    return read_trailer(ctx, node, layer, 256, out, n_chunks * 16);
+}
+
+int dissem_layer_received(dissem_ctx *ctx, int node, int layer, int64_t *bytes_out) {
+    if (!ctx || !bytes_out) return set_error(DISSEM_EINVAL, "dissem_layer_received: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    unsigned long long v = 0;
+    int rc = read_trailer(ctx, node, layer, 0, &v, 8);
+    if (rc) return rc;
+    *bytes_out = (int64_t)v;
+    return DISSEM_OK;
+}
+
+int dissem_layer_verify(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks) {
+    if (!ctx || (!out && n_chunks > 0)) return set_error(DISSEM_EINVAL, "dissem_layer_verify: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    if (n_chunks != lb->n_chunks()) return set_error(DISSEM_EINVAL, "layer %d has %lld chunks, caller passed %lld", layer, (long long)lb->n_chunks(), (long long)n_chunks);
+    if (n_chunks == 0) return DISSEM_OK;
+    for (auto &d : ctx->devs) {
+        CUDA_TRY(cudaSetDevice(d.dev));
+        CUDA_TRY(cudaStreamSynchronize(d.stream));
+    }
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    // scratch: a descriptor and a fresh checksum table
+    uint8_t *scratch = nullptr;
+    const size_t table_bytes = (size_t)n_chunks * 16;
+    CUDA_TRY(cudaMalloc(&scratch, 256 + table_bytes));
+    XferDesc d;
+    memset(&d, 0, sizeof d);
+    d.src = lb->base;
+    d.dst = nullptr;
+    d.csum = reinterpret_cast<unsigned long long *>(scratch + 256);
+    d.received = nullptr;
+    d.off = 0;
+    d.size = lb->size;
+    d.total = lb->size;
+    d.first_unit = 0;
+    int result = DISSEM_OK;
+    cudaError_t e = cudaMemsetAsync(scratch, 0, 256 + table_bytes, ds->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(scratch, &d, sizeof d, cudaMemcpyHostToDevice, ds->stream);
+    if (e == cudaSuccess) {
+        LaunchCfg cfg{ds->n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg};
+        e = launch_copy_csum(reinterpret_cast<XferDesc *>(scratch), 1, units_of(0, lb->size, kChunkShift), kChunkShift,
+                             ds->counters, cfg, ds->stream, nullptr);
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, scratch + 256, table_bytes, cudaMemcpyDeviceToHost, ds->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ds->stream);
+    if (e != cudaSuccess) result = set_error(DISSEM_ECUDA, "verify pass failed: %s", cudaGetErrorString(e));
+    cudaFree(scratch);
+    return result;
+}
+
+int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
+    if (!ctx || !key) return set_error(DISSEM_EINVAL, "dissem_set_option: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    std::string k(key);
+    if (k == "ctas_per_sm") { if (value < 0 || value > 32) return set_error(DISSEM_EINVAL, "ctas_per_sm out of range"); ctx->opt_ctas_per_sm = value; }
+    else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
+    else if (k == "reg_cfg") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..2"); ctx->opt_reg_cfg = value; }
+    else if (k == "unit_bytes") {
+        if (value != 0 && (value < 4096 || value > DISSEM_CHUNK_BYTES || (value & (value - 1)))) return set_error(DISSEM_EINVAL, "unit_bytes must be 0 or a power of two in [4096, 262144]");
+        ctx->opt_unit_bytes = value;
+    } else return set_error(DISSEM_EINVAL, "unknown option '%s'", key);
+    return DISSEM_OK;
+}
+
+int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out) {
+    if (!ctx || !key || !value_out) return set_error(DISSEM_EINVAL, "dissem_get_option: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    std::string k(key);
+    if (k == "ctas_per_sm") *value_out = ctx->opt_ctas_per_sm;
+    else if (k == "variant") *value_out = ctx->opt_variant;
+    else if (k == "reg_cfg") *value_out = ctx->opt_reg_cfg;
+    else if (k == "unit_bytes") *value_out = ctx->opt_unit_bytes;
+    else return set_error(DISSEM_EINVAL, "unknown option '%s'", key);
+    return DISSEM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,26 @@
+// Internal host-side types shared by the engine and the host mirror.  Not part of the C ABI.
+#pragma once
+#include <stdint.h>
+
+namespace dissem {
+
+int set_error(int code, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
+const char *last_error();
+
+// One layer of one node's store (LayerSrc, distributor/node.go:200-211) as an HBM buffer:
+// [ layer bytes | pad to 4 KiB | received counter (256 B slot) | checksum table: 16 B per chunk ]
+struct LayerBuf {
+    int64_t size = 0;
+    uint8_t *base = nullptr;
+    int device = -1;        // CUDA ordinal of the owning device; -1 for an imported (remote) layer
+    bool imported = false;
+
+    int64_t n_chunks() const;
+    int64_t trailer_off() const;
+    int64_t trailer_bytes() const;
+    int64_t alloc_bytes() const;
+    unsigned long long *received() const;
+    unsigned long long *csum() const;
+};
+
+}  // namespace dissem

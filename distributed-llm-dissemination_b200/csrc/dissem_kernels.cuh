@@ -1,0 +1,69 @@
+// Internal interface between the host engine (dissem_engine.cu) and the sm_100a kernels
+// (dissem_kernels.cu).  Not part of the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dissem {
+
+constexpr int kChunkShift = 18;                      // DISSEM_CHUNK_BYTES = 256 KiB
+constexpr long long kChunkBytes = 1ll << kChunkShift;
+
+enum : int {
+    kFlagMulticast = 1,   // dst / csum / received are NVLS multicast addresses (multimem.* only)
+};
+
+// One transfer as the kernels see it: bytes [off, off+size) of a layer, from the source copy to the
+// destination copy (distributor/transport.go:342: data[Offset : Offset+DataSize]).
+// Work units of a schedule are U-aligned slices of LAYER space (U = 1 << unit_shift <= 256 KiB), so a
+// unit never straddles a checksum chunk; first_unit is the exclusive prefix over the descriptor table.
+struct __align__(16) XferDesc {
+    const uint8_t *src;              // source layer base (local HBM)
+    uint8_t *dst;                    // destination layer base: local, peer-mapped or multicast; NULL = checksum only
+    unsigned long long *csum;        // destination checksum table (2 x u64 per chunk); NULL = none
+    unsigned long long *received;    // destination received-bytes counter; NULL = none
+    long long off;                   // fragment start within the layer
+    long long size;                  // fragment bytes (> 0)
+    long long total;                 // full layer size
+    long long first_unit;            // exclusive prefix of unit counts
+    int flags;
+    int pad[3];
+};
+static_assert(sizeof(XferDesc) == 80, "XferDesc layout");
+
+// Scratch the copy kernels need beyond their inputs and outputs: the work-unit ticket and the count of
+// CTAs that have drained (the last one re-arms both for the next launch).
+struct SchedCounters {
+    unsigned long long ticket;
+    unsigned int done_ctas;
+    unsigned int pad;
+};
+
+struct LaunchCfg {
+    int n_sm;
+    int ctas_per_sm;   // 0 = use the occupancy calculator
+    int variant;       // 0 register path, 1 TMA bulk-staged path
+    int reg_cfg;       // register-path shape: 0 = 256 thr x4, 1 = 512 thr x4, 2 = 256 thr x8
+};
+
+// Zero the checksum entries of every chunk a descriptor covers completely (so that launching the same
+// schedule again does not accumulate onto the previous run).  Chunks shared by several fragments are
+// zeroed by their owner (dissem_layer_alloc / dissem_layer_reset).
+cudaError_t launch_zero_csum(const XferDesc *descs, int n_descs, cudaStream_t stream);
+
+// The hot kernel: copy + fused per-chunk checksum (+ completion counter) over a descriptor table.
+cudaError_t launch_copy_csum(const XferDesc *descs, int n_descs, long long total_units, int unit_shift,
+                             SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream,
+                             int *grid_out);
+
+// Synthetic contents (DISSEM_FILL_PATTERN).
+cudaError_t launch_fill_pattern(uint8_t *dst, long long size, unsigned long long layer_id,
+                                unsigned long long seed, int n_sm, cudaStream_t stream);
+
+// Number of units a fragment occupies for a given unit size.
+static inline long long units_of(long long off, long long size, int unit_shift) {
+    if (size <= 0) return 0;
+    return ((off + size - 1) >> unit_shift) - (off >> unit_shift) + 1;
+}
+
+}  // namespace dissem

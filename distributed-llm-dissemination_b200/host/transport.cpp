@@ -1,0 +1,169 @@
+#include "transport.h"
+
+#include "../csrc/dissem_engine.h"
+
+namespace dissem {
+namespace host {
+
+void MsgChan::Push(MessagePtr m) {
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (closed_) return;
+        q_.push_back(std::move(m));
+    }
+    cv_.notify_one();
+}
+
+bool MsgChan::Pop(MessagePtr *out) {
+    std::unique_lock<std::mutex> lk(mu_);
+    cv_.wait(lk, [&] { return closed_ || !q_.empty(); });
+    if (q_.empty()) return false;
+    *out = std::move(q_.front());
+    q_.pop_front();
+    return true;
+}
+
+void MsgChan::Close() {
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        closed_ = true;
+    }
+    cv_.notify_all();
+}
+
+void DeviceFabric::Register(NodeID id, DeviceTransport *t) {
+    std::lock_guard<std::mutex> lk(mu_);
+    peers_[id] = t;
+}
+void DeviceFabric::Unregister(NodeID id) {
+    std::lock_guard<std::mutex> lk(mu_);
+    peers_.erase(id);
+}
+DeviceTransport *DeviceFabric::Lookup(NodeID id) {
+    std::lock_guard<std::mutex> lk(mu_);
+    auto it = peers_.find(id);
+    return it == peers_.end() ? nullptr : it->second;
+}
+std::vector<NodeID> DeviceFabric::Ids() {
+    std::lock_guard<std::mutex> lk(mu_);
+    std::vector<NodeID> v;
+    for (auto &kv : peers_) v.push_back(kv.first);
+    return v;
+}
+
+DeviceTransport::DeviceTransport(DeviceFabric *fabric, NodeID me) : fabric_(fabric), me_(me) {
+    fabric_->Register(me_, this);
+}
+DeviceTransport::~DeviceTransport() { Close(); }
+
+int DeviceTransport::Close() {
+    if (!closed_) {
+        closed_ = true;
+        fabric_->Unregister(me_);
+        inbox_.Close();
+    }
+    return 0;
+}
+
+int DeviceTransport::RegisterPipe(LayerID, NodeID) {
+    return set_error(DISSEM_ENOTSUP, "RegisterPipe: external-client tee forwarding is not part of the device transport");
+}
+
+int DeviceTransport::Broadcast(MessagePtr message) {
+    for (NodeID id : fabric_->Ids()) Send(id, message);      // errors are logged and dropped, transport.go:298-303
+    return 0;
+}
+
+int DeviceTransport::EnsureDestLayer(NodeID dest, LayerID layer, int64_t total) {
+    int rc = dissem_layer_info(fabric_->ctx(), (int)dest, (int)layer, nullptr, nullptr);
+    if (rc == DISSEM_ENOENT) {
+        rc = dissem_layer_alloc(fabric_->ctx(), (int)dest, (int)layer, total);
+        if (rc == DISSEM_EEXIST) rc = 0;          // another sender of the same layer got there first
+    }
+    return rc;
+}
+
+int DeviceTransport::Send(NodeID dest, MessagePtr message) {
+    DeviceTransport *peer = fabric_->Lookup(dest);
+    if (!peer) return set_error(DISSEM_ENOENT, "addr of %u does not exist", dest);     // transport.go:263-265
+    if (auto *lm = dynamic_cast<LayerMsg *>(message.get())) {
+        if (!lm->Src_.InDevice || lm->Src_.Meta.Location != InmemLayer)
+            return set_error(DISSEM_EINVAL, "unknown error sending layer %u", lm->Layer);   // transport.go:368-370
+        int rc = EnsureDestLayer(dest, lm->Layer, lm->TotalSize);
+        if (rc) return rc;
+        dissem_ticket ticket = 0;
+        rc = dissem_send(fabric_->ctx(), (int)lm->SrcID, (int)dest, (int)lm->Layer, lm->Src_.Offset, lm->Src_.DataSize,
+                         lm->TotalSize, &ticket);
+        if (rc) return rc;
+        double ms = 0.0;
+        rc = dissem_wait(fabric_->ctx(), ticket, &ms);          // Send returns when the bytes are written
+        if (rc) return rc;
+        {
+            std::lock_guard<std::mutex> lk(fabric_->stat_mu);
+            fabric_->layer_msgs++;
+            fabric_->layer_bytes += lm->Src_.DataSize;
+            fabric_->device_ms += ms;
+            fabric_->launches += lm->Src_.DataSize > 0 ? 2 : 0;
+        }
+        // what handleIncomingMsg hands to the node (transport.go:221-222): header fields + an in-memory LayerSrc
+        auto delivered = std::dynamic_pointer_cast<LayerMsg>(DecodeMsg(EncodeMsg(*lm)));
+        peer->inbox_.Push(delivered);
+        return 0;
+    }
+    {
+        std::lock_guard<std::mutex> lk(fabric_->stat_mu);
+        fabric_->control_msgs++;
+    }
+    peer->inbox_.Push(DecodeMsg(EncodeMsg(*message)));
+    return 0;
+}
+
+int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *device_ms_out) {
+    std::vector<dissem_xfer> xs;
+    for (auto &x : xfers) {
+        int rc = EnsureDestLayer(x.Dest, x.Layer, x.TotalSize);
+        if (rc) return rc;
+        dissem_xfer d;
+        d.src_node = (int32_t)x.Src;
+        d.dst_node = (int32_t)x.Dest;
+        d.layer = (int32_t)x.Layer;
+        d.flags = 0;
+        d.off = x.Offset;
+        d.size = x.DataSize;
+        d.total = x.TotalSize;
+        xs.push_back(d);
+    }
+    dissem_ticket ticket = 0;
+    int rc = dissem_schedule_submit(fabric_->ctx(), xs.data(), (int)xs.size(), &ticket);
+    if (rc) return rc;
+    double ms = 0.0;
+    rc = dissem_wait(fabric_->ctx(), ticket, &ms);
+    if (rc) return rc;
+    if (device_ms_out) *device_ms_out = ms;
+    {
+        std::lock_guard<std::mutex> lk(fabric_->stat_mu);
+        fabric_->device_ms += ms;
+        fabric_->launches += 2;
+    }
+    for (auto &x : xfers) {
+        DeviceTransport *peer = fabric_->Lookup(x.Dest);
+        if (!peer) return set_error(DISSEM_ENOENT, "addr of %u does not exist", x.Dest);
+        LayerMsg lm;
+        lm.SrcID = x.Src;
+        lm.Layer = x.Layer;
+        lm.Src_.InDevice = true;
+        lm.Src_.DataSize = x.DataSize;
+        lm.Src_.Offset = x.Offset;
+        lm.TotalSize = x.TotalSize;
+        {
+            std::lock_guard<std::mutex> lk(fabric_->stat_mu);
+            fabric_->layer_msgs++;
+            fabric_->layer_bytes += x.DataSize;
+        }
+        peer->inbox_.Push(DecodeMsg(EncodeMsg(lm)));
+    }
+    return 0;
+}
+
+}  // namespace host
+}  // namespace dissem

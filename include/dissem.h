@@ -1,0 +1,153 @@
+/*
+ * dissem.h — C ABI of libdissem.so, the B200-native layer-dissemination engine.
+ *
+ * This is the drop-in boundary for ONE path of ynishimi/distributed-llm-dissemination: moving layer
+ * bytes from the nodes that hold them to the nodes the Assignment names.  Every "node" of the reference
+ * is one GPU (or a slice of one GPU) and its layer store (`LayersSrc`, distributor/node.go:172) is a
+ * table of HBM buffers.  The entry points are what a cgo `DeviceTransport` implementing
+ * `distributor.Transport` (distributor/transport.go:18-25) binds — see INTEGRATION.md for the stub.
+ *
+ * Conventions: plain C, no CUDA or torch types.  Every function returns 0 on success or a negative
+ * DISSEM_E* code; dissem_last_error() returns a thread-local description of the last failure.  All
+ * functions are thread-safe (Transport.Send is called from many goroutines, node.go:343, :598).  Nothing
+ * here falls back to the CPU: without a usable CUDA device the compute entry points fail with
+ * DISSEM_ENODEV.
+ *
+ * Citations are paths under the reference tree (/root/reference).
+ */
+#ifndef DISSEM_H
+#define DISSEM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DISSEM_VERSION 1
+
+/* Checksum chunk: the reference's write quantum (BucketSize, distributor/transport.go:408). */
+#define DISSEM_CHUNK_BYTES 262144
+
+/* dissem_layer_fill kinds.  ZERO is what the reference's dummy layers contain (cmd/config.go:141, :161). */
+#define DISSEM_FILL_ZERO 0
+#define DISSEM_FILL_PATTERN 1 /* u64 word i of layer L = mix64(seed + (L+1)*0x9E3779B97F4A7C15 + i) */
+#define DISSEM_FILL_POISON 2  /* 0xA5 */
+
+#define DISSEM_OK 0
+#define DISSEM_EINVAL -1   /* bad argument */
+#define DISSEM_ENODEV -2   /* no usable CUDA device / driver */
+#define DISSEM_ECUDA -3    /* a CUDA call failed (message in dissem_last_error) */
+#define DISSEM_ENOENT -4   /* unknown node / layer / ticket / schedule */
+#define DISSEM_EEXIST -5   /* layer already present */
+#define DISSEM_ENOMEM -6
+#define DISSEM_ERANGE -7   /* offset/size outside the layer */
+#define DISSEM_ENOTSUP -8  /* capability missing on this box (e.g. NVLS multicast) */
+#define DISSEM_EPARSE -9   /* malformed config JSON */
+#define DISSEM_EPLAN -10   /* the mode cannot serve this placement (e.g. mode 0, leader lacks a layer) */
+
+typedef struct dissem_ctx dissem_ctx;
+typedef int64_t dissem_ticket;   /* one submitted batch of transfers */
+typedef int64_t dissem_sched;    /* one compiled schedule */
+
+/* One layerMsg on the wire (tempLayerInfo, distributor/transport.go:47-54): bytes [off, off+size) of
+ * `layer` go from src_node's copy to the same offsets of dst_node's copy; total = full layer size
+ * (LayerSize = size, TotalSize = total, Offert = off).  Modes 0/1 send whole layers (off = 0,
+ * size = total; node.go:363, :1478); mode 3 sends fragments (node.go:1604-1606). */
+typedef struct dissem_xfer {
+    int32_t src_node;
+    int32_t dst_node;
+    int32_t layer;
+    int32_t flags;   /* 0; reserved */
+    int64_t off;
+    int64_t size;
+    int64_t total;
+} dissem_xfer;
+
+/* ---- library ------------------------------------------------------------------------------------- */
+int dissem_version(void);
+const char *dissem_last_error(void);
+/* Number of CUDA devices visible to this process (0 when there is none; never an error). */
+int dissem_device_count(void);
+
+/* ---- context: stands for NewTcpTransport + the AddrRegistry (transport.go:56-95) ------------------ */
+/* device_of_node[i] >= 0: node i lives in THIS process on that CUDA device (several nodes may share a
+ * device: the 1-GPU configuration maps every node to device 0).  device_of_node[i] == -1: node i lives in
+ * another process (one process per GPU); its layers become reachable through dissem_layer_import.
+ * Peer access is enabled between all local devices. */
+int dissem_init(int n_nodes, const int *device_of_node, dissem_ctx **out);
+int dissem_close(dissem_ctx *ctx); /* Transport.Close, transport.go:474-491 */
+int dissem_n_nodes(dissem_ctx *ctx);
+
+/* ---- layer store: LayersSrc / LayerSrc (node.go:172, :200-211), CreateInmemLayer (config.go:159-171) - */
+/* Allocates an HBM buffer for `layer` on a local node.  The buffer carries a trailer with the layer's
+ * per-chunk checksum table and its received-bytes counter (both zeroed). */
+int dissem_layer_alloc(dissem_ctx *ctx, int node, int layer, int64_t size);
+int dissem_layer_free(dissem_ctx *ctx, int node, int layer);
+/* size_out / device_ptr_out may be NULL.  DISSEM_ENOENT if the node does not hold the layer. */
+int dissem_layer_info(dissem_ctx *ctx, int node, int layer, int64_t *size_out, void **device_ptr_out);
+/* Synthesise contents on the GPU (DISSEM_FILL_*); asynchronous on the node's stream. */
+int dissem_layer_fill(dissem_ctx *ctx, int node, int layer, int kind, uint64_t seed);
+/* Zero the checksum table and the received counter (a destination does this before a new run). */
+int dissem_layer_reset(dissem_ctx *ctx, int node, int layer);
+/* Host <-> HBM.  `host` may be any host memory; pinned memory from dissem_host_alloc makes the copy
+ * asynchronous and full-speed.  write is ordered before later transfers on the node's stream; read
+ * waits for everything submitted so far on the node's device. */
+int dissem_layer_write(dissem_ctx *ctx, int node, int layer, const void *host, int64_t off, int64_t size);
+int dissem_layer_read(dissem_ctx *ctx, int node, int layer, void *host, int64_t off, int64_t size);
+int dissem_host_alloc(void **out, int64_t size); /* pinned host memory for layer bytes */
+int dissem_host_free(void *p);
+
+/* ---- one process per GPU: make a local layer reachable from peer processes -------------------------- */
+/* handle_out: 64 opaque bytes to ship over the control plane (e.g. inside the announceMsg, message.go:31-41). */
+int dissem_layer_export(dissem_ctx *ctx, int node, int layer, uint8_t handle_out[64]);
+/* Map a remote node's layer (allocated by its owner process) so that local nodes can push into it. */
+int dissem_layer_import(dissem_ctx *ctx, int node, int layer, int64_t size, const uint8_t handle[64]);
+
+/* ---- the hot path: TcpTransport.Send layer branch + sendLayerMsg + writeWithLimit on the sender
+ *      (transport.go:258-275, :308-373, :407-424) and handleIncomingMsg layer branch on the receiver
+ *      (transport.go:127-224), as one push kernel per source GPU with the checksum fused in ----------- */
+/* Asynchronous.  The destination layer must exist (alloc or import).  Only transfers whose src_node is
+ * local to this process are executed; others are skipped (their owner process runs them). */
+int dissem_send(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t off, int64_t size,
+                int64_t total, dissem_ticket *out);
+/* A whole plan at once (what LeaderNode.sendLayers / RetransmitLeaderNode.sendLayers / dispatchJob issue
+ * one goroutine at a time, node.go:326-352, :554-626, :1237-1288): compiled into one launch per source
+ * GPU.  dissem_schedule_submit = compile + launch + free. */
+int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_ticket *out);
+int dissem_schedule_compile(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_sched *out);
+int dissem_schedule_launch(dissem_ctx *ctx, dissem_sched sched, dissem_ticket *out);
+int dissem_schedule_free(dissem_ctx *ctx, dissem_sched sched);
+/* units_out: work units of the compiled schedule; launches_out: kernel launches one dissem_schedule_launch
+ * issues; bytes_out: bytes the local sources deliver. */
+int dissem_schedule_info(dissem_ctx *ctx, dissem_sched sched, int64_t *units_out, int *launches_out,
+                         int64_t *bytes_out);
+/* Block until the batch is complete (all bytes visible at their destinations).  ms_out (may be NULL):
+ * device time of the batch, max over the source GPUs involved.  The ticket is consumed. */
+int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out);
+/* As dissem_wait; copy_ms_out (may be NULL) is the device time of the copy+checksum kernel alone (the batch
+ * also runs a tiny kernel that zeroes the checksum entries it is about to fill). */
+int dissem_wait_detail(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out, double *copy_ms_out);
+int dissem_poll(dissem_ctx *ctx, dissem_ticket ticket, int *done_out);
+
+/* ---- delivery verification (no counterpart in the reference, which never checks content) ----------- */
+/* Per-chunk checksums accumulated by the copy pass at the DESTINATION copy of the layer:
+ * out[2c] = A_c, out[2c+1] = B_c, n_chunks = ceil(size / DISSEM_CHUNK_BYTES).  Definition in DESIGN.md §4. */
+int dissem_layer_checksums(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks);
+/* Independent read-only pass over the layer as it now sits in HBM; same format. */
+int dissem_layer_verify(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks);
+/* Bytes received so far for the layer (the counter FlowRetransmitReceiverNode keeps in
+ * layerSrc.DataSize, node.go:1542; the ack condition is received == total, node.go:1555). */
+int dissem_layer_received(dissem_ctx *ctx, int node, int layer, int64_t *bytes_out);
+
+/* ---- tuning / introspection -------------------------------------------------------------------------- */
+/* key: "ctas_per_sm" (0 = occupancy-derived), "variant" (0 = register path, 1 = TMA bulk-staged path),
+ * "reg_cfg" (register-path shape: 0 = 256 threads x4 loads in flight, 1 = 512 x4, 2 = 256 x8),
+ * "unit_bytes" (0 = auto; else power of two in [4096, 262144]). */
+int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value);
+int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DISSEM_H */

@@ -1,0 +1,297 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (include/dissem.h), against the CPU oracle on
+the same seeded inputs; against the committed golden vectors; and, at BASELINE.json's full sizes, through
+size-independent properties.  Bar: bit-exact (this path is byte/integer work only)."""
+import importlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import dissem_b200 as d
+from oracle import c_oracle as co
+from oracle import dissem_oracle as o
+
+pytestmark = pytest.mark.gpu
+host = importlib.import_module("distributed-llm-dissemination_b200.host")
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+SEED = 0x5EED
+
+RAGGED = [0, 1, 3, 4, 5, 15, 16, 17, 31, 4095, 4096, 4097, 262143, 262144, 262145, 786432 + 13, (1 << 20) + 5]
+
+
+@pytest.fixture()
+def eng():
+    e = d.Engine([0, 0, 0, 0])
+    yield e
+    e.close()
+
+
+# ---- K6 fill, K5 verify ------------------------------------------------------------------------------
+@pytest.mark.parametrize("size", RAGGED)
+def test_fill_and_verify_match_oracle(eng, size):
+    for kind in (d.FILL_ZERO, d.FILL_PATTERN, d.FILL_POISON):
+        eng.alloc(0, 7, size)
+        eng.fill(0, 7, kind, SEED)
+        want = o.fill_bytes(kind, 7, size, SEED)
+        assert np.array_equal(eng.read(0, 7), want)
+        assert np.array_equal(eng.verify(0, 7), o.checksum(want))
+        eng.free(0, 7)
+
+
+def test_golden_checksum_vectors(eng):
+    gold = json.load(open(os.path.join(GOLD, "checksum_kat.json")))
+    assert gold["chunk_bytes"] == d.CHUNK_BYTES
+    for i, case in enumerate(gold["cases"]):
+        eng.alloc(2, case["layer"], case["size"])
+        eng.fill(2, case["layer"], case["kind"], case["seed"])
+        got = eng.verify(2, case["layer"])
+        assert [[int(a), int(b)] for a, b in got.tolist()] == case["csum"]
+        assert o.digest(got) == case["digest"]
+        assert eng.read(2, case["layer"])[:16].tobytes().hex() == case["head_hex"]
+        eng.free(2, case["layer"])
+
+
+# ---- K1/K4 whole-layer send ----------------------------------------------------------------------------
+@pytest.mark.parametrize("size", [s for s in RAGGED if s > 0] + [o.S2])
+def test_send_whole_layer_bit_exact(eng, size):
+    eng.alloc(0, 3, size)
+    eng.fill(0, 3, d.FILL_PATTERN, SEED)
+    eng.alloc(1, 3, size)
+    eng.fill(1, 3, d.FILL_POISON)
+    ms = eng.wait(eng.send(0, 1, 3, 0, size, size))
+    assert ms >= 0.0
+    want = co.fill_bytes(o.FILL_PATTERN, 3, size, SEED)
+    assert np.array_equal(eng.read(1, 3), want)
+    assert np.array_equal(eng.read(0, 3), want)                       # the source is untouched
+    cs = co.checksum(want)
+    assert np.array_equal(eng.checksums(1, 3), cs)                    # fused pass
+    assert np.array_equal(eng.verify(1, 3), cs)                       # independent re-read
+    assert eng.received(1, 3) == size
+
+
+def test_empty_layer_and_reference_zero_layers(eng):
+    eng.alloc(0, 1, 0)
+    eng.alloc(1, 1, 0)
+    eng.wait(eng.send(0, 1, 1, 0, 0, 0))
+    assert eng.read(1, 1).size == 0 and eng.checksums(1, 1).shape == (0, 2)
+    # the reference's dummy layers are all zero (cmd/config.go:141, :161): A = B = 0, destination turns from poison to zero
+    size = 3 * d.CHUNK_BYTES + 77
+    eng.alloc(0, 2, size)
+    eng.fill(0, 2, d.FILL_ZERO)
+    eng.alloc(1, 2, size)
+    eng.fill(1, 2, d.FILL_POISON)
+    eng.wait(eng.send(0, 1, 2, 0, size, size))
+    assert not eng.read(1, 2).any() and not eng.checksums(1, 2).any() and eng.received(1, 2) == size
+
+
+# ---- fragments (mode 3): arbitrary byte offsets, several sources, placement at the offset -----------------
+@pytest.mark.parametrize("cuts", [
+    [0, 1, 2, 3],
+    [0, 5, 262144 - 3, 262144 + 7, 600_001],
+    [0, 16, 4096, 300_000, 786_445],
+    [0, 333_333, 333_334, 1_000_003],
+])
+def test_fragments_from_several_sources(eng, cuts):
+    size = cuts[-1]
+    layer = 11
+    want = o.fill_bytes(o.FILL_PATTERN, layer, size, SEED)
+    for n in (0, 1, 2):
+        eng.alloc(n, layer, size)
+        eng.fill(n, layer, d.FILL_PATTERN, SEED)
+    eng.alloc(3, layer, size)
+    eng.fill(3, layer, d.FILL_POISON)
+    frags = [(i % 3, 3, layer, a, b - a, size) for i, (a, b) in enumerate(zip(cuts, cuts[1:]))]
+    # all but the last fragment: what is missing must still be poison, the counter must say so
+    eng.wait(eng.submit(frags[:-1]))
+    got = eng.read(3, layer)
+    a_last = cuts[-2]
+    assert np.array_equal(got[:a_last], want[:a_last]) and (got[a_last:] == o.POISON_BYTE).all()
+    assert eng.received(3, layer) == a_last
+    eng.wait(eng.submit(frags[-1:]))
+    assert np.array_equal(eng.read(3, layer), want)
+    assert np.array_equal(eng.checksums(3, layer), o.checksum(want))
+    assert eng.received(3, layer) == size
+
+
+def test_misplaced_fragment_is_caught_by_B(eng):
+    size = 2 * d.CHUNK_BYTES
+    eng.alloc(0, 5, size)
+    eng.fill(0, 5, d.FILL_PATTERN, SEED)
+    eng.alloc(1, 5, size)
+    src = eng.read(0, 5)
+    swapped = src.copy()
+    swapped[4096:8192], swapped[8192:12288] = src[8192:12288].copy(), src[4096:8192].copy()
+    eng.write(1, 5, swapped)
+    got, ref = eng.verify(1, 5), eng.verify(0, 5)
+    assert got[0, 0] == ref[0, 0] and got[0, 1] != ref[0, 1] and np.array_equal(got[1], ref[1])
+    assert np.array_equal(got, o.checksum(swapped))
+
+
+# ---- whole plans -----------------------------------------------------------------------------------------
+def _materialise(eng, cfg, fill=d.FILL_PATTERN, seed=SEED):
+    for n in cfg.nodes:
+        for l, (size, _) in n.layers.items():
+            eng.alloc(n.id, l, size)
+            eng.fill(n.id, l, fill, seed)
+
+
+def _alloc_destinations(eng, xfers):
+    for x in xfers:
+        if not eng.has(x.dst_node, x.layer):
+            eng.alloc(x.dst_node, x.layer, x.total)
+            eng.fill(x.dst_node, x.layer, d.FILL_POISON)
+
+
+@pytest.mark.parametrize("mode,policy", [(0, 0), (1, 0), (1, 1), (3, 0)])
+@pytest.mark.parametrize("unit_bytes", [0, 4096, 65536, 262144])
+def test_plan_schedule_matches_oracle_store(mode, policy, unit_bytes):
+    size = (1 << 20) + 4 * 17          # ragged layer size, not a multiple of the chunk
+    text = o.config_stage_ring(8, 32, size, ring=(mode != 0))
+    cfg = o.parse_config(text)
+    p = d.plan(text, mode, seed=SEED, policy=policy, time_scale=1_000_000)
+    xfers = d.parse_plan(p)
+    with d.Engine([0] * 8) as eng:
+        eng.set_option("unit_bytes", unit_bytes)
+        _materialise(eng, cfg)
+        _alloc_destinations(eng, xfers)
+        eng.wait(eng.submit(xfers))
+        want = o.apply_transfers(o.initial_store(cfg, o.FILL_PATTERN, SEED),
+                                 [o.Xfer(x.src_node, x.dst_node, x.layer, x.off, x.size, x.total) for x in xfers])
+        assert o.assignment_satisfied(cfg, want)
+        for (node, layer), data in want.items():
+            assert np.array_equal(eng.read(node, layer), data), (node, layer)
+        for x in xfers:
+            assert np.array_equal(eng.checksums(x.dst_node, x.layer), o.checksum(want[(x.dst_node, x.layer)]))
+            assert eng.received(x.dst_node, x.layer) == x.total
+
+
+@pytest.mark.parametrize("reg_cfg", [0, 1, 2])
+def test_kernel_shapes_agree(reg_cfg):
+    size = 5 * d.CHUNK_BYTES + 123
+    with d.Engine([0, 0]) as eng:
+        eng.set_option("reg_cfg", reg_cfg)
+        eng.alloc(0, 0, size)
+        eng.fill(0, 0, d.FILL_PATTERN, 9)
+        eng.alloc(1, 0, size)
+        eng.fill(1, 0, d.FILL_POISON)
+        eng.wait(eng.send(0, 1, 0, 0, size, size))
+        want = o.fill_bytes(o.FILL_PATTERN, 0, size, 9)
+        assert np.array_equal(eng.read(1, 0), want) and np.array_equal(eng.checksums(1, 0), o.checksum(want))
+
+
+def test_relaunching_a_compiled_schedule_is_idempotent():
+    size = 4 * d.CHUNK_BYTES
+    with d.Engine([0, 0, 0]) as eng:
+        for l in range(4):
+            eng.alloc(0, l, size)
+            eng.fill(0, l, d.FILL_PATTERN, 1)
+            eng.alloc(1 + l % 2, l, size)
+        s = eng.compile([(0, 1 + l % 2, l, 0, size, size) for l in range(4)])
+        units, launches, nbytes = eng.sched_info(s)
+        assert nbytes == 4 * size and launches == 2 and units >= 16
+        first = None
+        for _ in range(3):
+            eng.wait(eng.launch(s))
+            tables = [eng.checksums(1 + l % 2, l).copy() for l in range(4)]
+            if first is None:
+                first = tables
+            assert all(np.array_equal(a, b) for a, b in zip(first, tables))
+        for l in range(4):
+            assert np.array_equal(first[l], o.checksum(o.fill_bytes(o.FILL_PATTERN, l, size, 1)))
+            assert eng.received(1 + l % 2, l) == 3 * size          # the counter is monotonic across runs
+        eng.sched_free(s)
+
+
+# ---- BASELINE.json sizes: properties that do not need the oracle to hold the whole store -------------------
+def test_config2_full_size_properties():
+    """8 nodes, 32 layers x 64 MiB, mode 1 (BASELINE config 2) on one GPU: every destination's fused table
+    equals an independent re-read of the destination and of the source, and the C oracle's table."""
+    text = o.config_stage_ring(8, 32, o.S2)
+    cfg = o.parse_config(text)
+    xfers = d.parse_plan(d.plan(text, 1, seed=SEED))
+    assert sum(x.size for x in xfers) == 1_879_048_192
+    with d.Engine([0] * 8) as eng:
+        _materialise(eng, cfg)
+        _alloc_destinations(eng, xfers)
+        eng.wait(eng.submit(xfers))
+        ref = {}
+        for x in xfers:
+            if x.layer not in ref:
+                ref[x.layer] = co.checksum(co.fill_bytes(o.FILL_PATTERN, x.layer, o.S2, SEED))
+            fused = eng.checksums(x.dst_node, x.layer)
+            assert np.array_equal(fused, ref[x.layer])
+            assert np.array_equal(eng.verify(x.dst_node, x.layer), fused)
+            assert np.array_equal(eng.verify(x.src_node, x.layer), fused)
+            assert eng.received(x.dst_node, x.layer) == o.S2
+
+
+@pytest.mark.parametrize("size", [o.S8B, 218_112_000, o.S70B])
+def test_llama_layer_sizes_round_trip(size):
+    """One Llama-3-8B / 70B-shaped layer: copy, then checksum-of-checksums against the C oracle."""
+    with d.Engine([0, 0]) as eng:
+        eng.alloc(0, 79, size)
+        eng.fill(0, 79, d.FILL_PATTERN, SEED)
+        eng.alloc(1, 79, size)
+        eng.fill(1, 79, d.FILL_POISON)
+        eng.wait(eng.send(0, 1, 79, 0, size, size))
+        data = co.fill_bytes(o.FILL_PATTERN, 79, size, SEED)
+        want = co.checksum(data)
+        fused = eng.checksums(1, 79)
+        assert o.digest(fused) == o.digest(want)
+        assert o.digest(eng.verify(1, 79)) == o.digest(want)
+        assert np.array_equal(eng.read(1, 79, off=size - 4096, size=4096), data[-4096:])
+        assert np.array_equal(eng.read(1, 79, off=0, size=4096), data[:4096])
+        assert eng.received(1, 79) == size
+
+
+# ---- the reference's own fixtures through the C++ role state machines --------------------------------------
+@pytest.mark.parametrize("batched", [False, True])
+@pytest.mark.parametrize("mode,fixture", [(0, "identity"), (1, "ring"), (0, "readme"), (1, "readme"), (3, "ring")])
+def test_reference_fixtures_through_roles(mode, fixture, batched):
+    """node_test.go:163-273 (TestSimpleDistribution inmem/tcp/tcp_retransmission) with 1-byte layers, plus the
+    README config: Ready() fires with the assignment; here the bytes are checked as well."""
+    text = {"identity": o.config_identity_fixture, "ring": o.config_ring_fixture, "readme": o.config_readme}[fixture]()
+    flags = host.PLAN_ZERO_RATE_UNLIMITED if fixture == "readme" else 0
+    if mode == 3 and fixture == "readme":
+        pytest.skip("README config has no NetworkBW")
+    r = host.run_distribution(text, mode, batched=batched, seed=SEED, time_scale=1_000_000, flags=flags, timeout_ms=10000)
+    assert r["ready_equals_assignment"] and r["verified"]
+    cfg = o.parse_config(text)
+    if mode == 0:
+        want = o.plan_mode0(cfg)
+        assert [tuple(x) for x in r["xfers"]] == [(x.src, x.dst, x.layer, x.off, x.size, x.total) for x in want]
+    elif mode == 1:
+        cand = o.mode1_owner_candidates(cfg)
+        assert len(r["xfers"]) == len(cand)
+        for (s, dst, l, *_r) in r["xfers"]:
+            assert s in cand[(dst, l)]
+    assert r["layer_msgs"] == len(r["xfers"]) and r["bytes"] == sum(x[4] for x in r["xfers"])
+
+
+@pytest.mark.parametrize("mode", [0, 1, 3])
+def test_roles_move_real_layers(mode):
+    text = o.config_stage_ring(4, 8, 3 * d.CHUNK_BYTES + 1001, ring=(mode == 1))
+    r = host.run_distribution(text, mode, batched=False, seed=SEED, time_scale=1_000_000, timeout_ms=20000)
+    assert r["verified"] and r["layers_checked"] == 6 and r["ready_equals_assignment"]
+    rb = host.run_distribution(text, mode, batched=True, seed=SEED, time_scale=1_000_000, timeout_ms=20000)
+    assert rb["verified"] and rb["xfers"] == r["xfers"] and rb["launches"] == 2
+
+
+# ---- error behaviour ---------------------------------------------------------------------------------------
+def test_errors(eng):
+    eng.alloc(0, 1, 100)
+    with pytest.raises(d.DissemError) as e:
+        eng.send(0, 1, 1, 0, 100, 100)          # destination layer missing
+    assert e.value.code == -4
+    eng.alloc(1, 1, 100)
+    with pytest.raises(d.DissemError) as e:
+        eng.send(0, 1, 1, 50, 100, 100)         # outside the layer
+    assert e.value.code == -7
+    with pytest.raises(d.DissemError) as e:
+        eng.alloc(0, 1, 100)
+    assert e.value.code == -5
+    with pytest.raises(d.DissemError):
+        eng.send(0, 9, 1, 0, 100, 100)          # no such node
+    with pytest.raises(d.DissemError):
+        eng.wait(12345)

@@ -1,0 +1,165 @@
+"""CPU tests of the product's host side: the C ABI loads and exports every declared symbol, the C++ plan
+generators agree with the oracle on every config/mode, and the control-plane wire format matches the
+reference's.  No compute entry point is called: there is no GPU here."""
+import importlib
+import json
+import os
+import re
+
+import pytest
+
+import dissem_b200 as d
+from oracle import dissem_oracle as o
+
+host = importlib.import_module("distributed-llm-dissemination_b200.host")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    names = []
+    for hdr in ("dissem.h", "dissem_host.h"):
+        text = open(os.path.join(ROOT, "include", hdr)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names += re.findall(r"\b(dissem_[a-z0-9_]+)\s*\(", text)
+    return sorted(set(names))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    L = d.load_library()
+    syms = _declared_symbols()
+    assert len(syms) >= 30
+    for name in syms:
+        assert hasattr(L, name), f"{name} declared in include/ but not exported"
+    assert L.dissem_version() == 1
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    assert d.lib().dissem_device_count() == 0
+    with pytest.raises(d.DissemError) as e:
+        d.Engine([0, 0])
+    assert e.value.code == -2 and "no CPU path" in str(e.value)
+    with pytest.raises(d.DissemError):
+        host.run_distribution(o.config_readme(), 0)
+
+
+def _rows(plan):
+    return [tuple(x[:6]) for x in plan["xfers"]]
+
+
+def _orows(xs):
+    return [(x.src, x.dst, x.layer, x.off, x.size, x.total) for x in xs]
+
+
+CONFIGS = {
+    "readme": o.config_readme,
+    "identity": o.config_identity_fixture,
+    "ring": o.config_ring_fixture,
+    "stage_ring_8x32": lambda: o.config_stage_ring(8, 32, o.S2),
+    "stage_seed_8x32_8B": lambda: o.config_stage_ring(8, 32, o.S8B, ring=False),
+    "stage_ring_4x8": lambda: o.config_stage_ring(4, 8, 1 << 20),
+    "stage_ring_2x8": lambda: o.config_stage_ring(2, 8, 12345),
+}
+
+
+@pytest.mark.parametrize("name", sorted(CONFIGS))
+def test_mode0_plan_matches_oracle(name):
+    text = CONFIGS[name]()
+    assert _rows(d.plan(text, 0)) == _orows(o.plan_mode0(o.parse_config(text)))
+
+
+@pytest.mark.parametrize("name", sorted(CONFIGS))
+@pytest.mark.parametrize("policy", [0, 1])
+def test_mode1_plan_matches_oracle(name, policy):
+    text = CONFIGS[name]()
+    for seed in (0, 1, 0x5EED, 2**63 + 11):
+        got = _rows(d.plan(text, 1, seed=seed, policy=policy))
+        want = _orows(o.plan_mode1(o.parse_config(text), seed=seed, policy="balanced" if policy else "random"))
+        assert got == want
+        cand = o.mode1_owner_candidates(o.parse_config(text))      # and every pick is a valid owner
+        for (s, dst, l, *_rest) in got:
+            assert s in cand[(dst, l)]
+
+
+def test_mode1_fanout_config():
+    text = o.config_fanout()
+    got = _rows(d.plan(text, 1, seed=3))
+    assert got == _orows(o.plan_mode1(o.parse_config(text), seed=3)) and len(got) == 239
+    with pytest.raises(d.DissemError) as e:
+        d.plan(text, 0)
+    assert e.value.code == -10
+
+
+def test_mode3_flow_kat_and_oracle_agreement():
+    p = d.plan(o.config_conf_json(), 3)
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "flow_conf_json.json")))
+    assert p["t"] == gold["t"] == 60
+    assert [list(r) for r in _rows(p)] == gold["xfers"]
+    assert all(x[6] == x[4] // 60 for x in p["xfers"])          # rate = dataSize / minTime, node.go:1281
+
+
+@pytest.mark.parametrize("scale", [1, 1000, 1_000_000])
+@pytest.mark.parametrize("name", ["stage_seed_8x32_8B", "stage_ring_8x32", "stage_ring_4x8"])
+def test_mode3_matches_oracle_across_time_scales(name, scale):
+    text = CONFIGS[name]()
+    p = d.plan(text, 3, time_scale=scale)
+    t, xs, self_jobs = o.plan_mode3(o.parse_config(text), time_scale=scale)
+    assert p["t"] == t and _rows(p) == _orows(xs)
+    assert [tuple(j) for j in p["self_jobs"]] == [(n, l, s) for (n, l, s, _off) in self_jobs]
+
+
+def test_mode3_zero_rate_and_sizes_extensions():
+    text = o.config_readme()                                    # no Sources: LimitRate 0 everywhere
+    with pytest.raises(d.DissemError):
+        d.plan(text, 3)                                         # "tUpper not found", flow.go:162-165
+    cfg = json.loads(text)
+    for n in cfg["Nodes"]:
+        n["NetworkBW"] = 1000
+    text = json.dumps(cfg)
+    p = d.plan(text, 3, flags=1)
+    t, xs, _ = o.plan_mode3(o.parse_config(text), zero_rate_unlimited=True)
+    assert p["t"] == t and _rows(p) == _orows(xs)
+
+
+def test_bad_inputs_fail_loudly():
+    with pytest.raises(d.DissemError) as e:
+        d.plan("{not json", 0)
+    assert e.value.code == -9
+    with pytest.raises(d.DissemError) as e:
+        d.plan(json.dumps({"Nodes": [{"Id": 0}], "Assignment": {}}), 0)
+    assert e.value.code == -10 and "no leader" in str(e.value)
+    with pytest.raises(d.DissemError):
+        d.plan(o.config_readme(), 2)
+    with pytest.raises(d.DissemError):
+        d.plan(o.config_readme(), 7)                            # "unknown mode", cmd/main.go:163-164
+
+
+def test_schema_detection():
+    assert d.plan(o.config_readme(), 0)["flat_schema"] is True
+    assert d.plan(o.config_conf_json(), 3)["flat_schema"] is False
+    # Go's decoder is case-insensitive on field names: "Id" fills ID (cmd/config.go:22)
+    text = o.config_readme().replace('"Id"', '"ID"').replace('"IsLeader"', '"isleader"')
+    assert _rows(d.plan(text, 0)) == _rows(d.plan(o.config_readme(), 0))
+
+
+# ---- wire format, SURVEY Appendix A ----------------------------------------------------------------
+def test_wire_format_known_answers():
+    w, dec = host.msg_roundtrip(kind="announce", SrcID=1,
+                                LayerIDs={"4": {"Location": 0, "LimitRate": 0, "SourceType": 0}})
+    assert w == '{"type":0,"src":"1","payload":{"SrcID":1,"LayerIDs":{"4":{"Location":0,"LimitRate":0,"SourceType":0}}}}'
+    w, dec = host.msg_roundtrip(kind="ack", SrcID=1, LayerID=1, location=1)
+    assert w == '{"type":1,"src":"1","payload":{"SrcID":1,"LayerID":1}}'
+    assert dec["location_after_decode"] == 0          # unexported field: always decodes as in-memory (message.go:62-66)
+    w, _ = host.msg_roundtrip(kind="retransmit", SrcID=0, LayerID=1, DestID=2)
+    assert w == '{"type":3,"src":"0","payload":{"SrcID":0,"LayerID":1,"DestID":2}}'
+    w, _ = host.msg_roundtrip(kind="flowRetransmit", SrcID=0, LayerID=1, DestID=7, DataSize=5, Offset=6, Rate=7)
+    assert w == '{"type":4,"src":"0","payload":{"SrcID":0,"LayerID":1,"DestID":7,"DataSize":5,"Offset":6,"Rate":7}}'
+    w, _ = host.msg_roundtrip(kind="startup", SrcID=0)
+    assert w == '{"type":6,"src":"0","payload":{"SrcID":0}}'
+    w, dec = host.msg_roundtrip(kind="simple", SrcAddr="a:1", PayloadStr='he said "hi"\n')
+    assert json.loads(w)["payload"] == {"SrcAddr": "a:1", "PayloadStr": 'he said "hi"\n'} and dec["type"] == 7
+    w, dec = host.msg_roundtrip(kind="layerHeader", SrcID=0, LayerID=1, LayerSize=10, TotalSize=30, Offert=20)
+    assert w == '{"type":2,"src":"0","payload":{"SrcID":0,"LayerID":1,"LayerSize":10,"TotalSize":30,"Offert":20}}'
+    assert dec["payload"]["Offert"] == 20             # the offset survives (the reference drops it, transport.go:221)
