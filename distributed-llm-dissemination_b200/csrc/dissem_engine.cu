@@ -100,7 +100,7 @@ struct dissem_ctx {
     std::map<int64_t, Ticket> tickets;
     int64_t next_id = 1;
     // options
-    int64_t opt_ctas_per_sm = 0, opt_variant = 0, opt_unit_bytes = 0, opt_reg_cfg = 0;
+    int64_t opt_ctas_per_sm = 0, opt_variant = 0, opt_unit_bytes = 0, opt_reg_cfg = 1;
 };
 
 namespace dissem {
@@ -768,7 +768,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     std::string k(key);
     if (k == "ctas_per_sm") { if (value < 0 || value > 32) return set_error(DISSEM_EINVAL, "ctas_per_sm out of range"); ctx->opt_ctas_per_sm = value; }
     else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
-    else if (k == "reg_cfg") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..2"); ctx->opt_reg_cfg = value; }
+    else if (k == "reg_cfg") { if (value < 0 || value > 6) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..6"); ctx->opt_reg_cfg = value; }
     else if (k == "unit_bytes") {
         if (value != 0 && (value < 4096 || value > DISSEM_CHUNK_BYTES || (value & (value - 1)))) return set_error(DISSEM_EINVAL, "unit_bytes must be 0 or a power of two in [4096, 262144]");
         ctx->opt_unit_bytes = value;

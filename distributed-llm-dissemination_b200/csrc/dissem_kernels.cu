@@ -289,9 +289,13 @@ cudaError_t launch_copy_csum(const XferDesc *descs, int n_descs, long long total
     if (cfg.variant == 1)
         return launch_copy_csum_tma(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
     switch (cfg.reg_cfg) {
-        case 1: return launch_reg<512, 4>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 0: return launch_reg<256, 4>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
         case 2: return launch_reg<256, 8>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
-        default: return launch_reg<256, 4>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 3: return launch_reg<512, 8>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 4: return launch_reg<1024, 4>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 5: return launch_reg<1024, 2>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 6: return launch_reg<512, 2>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        default: return launch_reg<512, 4>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
     }
 }
 

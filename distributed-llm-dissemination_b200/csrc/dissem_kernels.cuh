@@ -43,7 +43,7 @@ struct LaunchCfg {
     int n_sm;
     int ctas_per_sm;   // 0 = use the occupancy calculator
     int variant;       // 0 register path, 1 TMA bulk-staged path
-    int reg_cfg;       // register-path shape: 0 = 256 thr x4, 1 = 512 thr x4, 2 = 256 thr x8
+    int reg_cfg;       // register-path shape (threads x loads in flight): 0 256x4, 1 512x4 (default), 2 256x8, 3 512x8, 4 1024x4, 5 1024x2, 6 512x2
 };
 
 // Zero the checksum entries of every chunk a descriptor covers completely (so that launching the same

@@ -142,7 +142,8 @@ int dissem_layer_received(dissem_ctx *ctx, int node, int layer, int64_t *bytes_o
 
 /* ---- tuning / introspection -------------------------------------------------------------------------- */
 /* key: "ctas_per_sm" (0 = occupancy-derived), "variant" (0 = register path, 1 = TMA bulk-staged path),
- * "reg_cfg" (register-path shape: 0 = 256 threads x4 loads in flight, 1 = 512 x4, 2 = 256 x8),
+ * "reg_cfg" (register-path shape, threads x 16-byte loads in flight: 0 256x4, 1 512x4 (default), 2 256x8,
+ * 3 512x8, 4 1024x4, 5 1024x2, 6 512x2),
  * "unit_bytes" (0 = auto; else power of two in [4096, 262144]). */
 int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value);
 int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out);
