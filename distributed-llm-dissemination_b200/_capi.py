@@ -78,6 +78,7 @@ def load_library() -> ctypes.CDLL:
         "dissem_layer_checksums": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
         "dissem_layer_verify": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
         "dissem_layer_received": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(i64)]),
+        "dissem_checksum_noalloc": (c.c_int, [c.c_int, P, i64, P, i64, P]),
         "dissem_set_option": (c.c_int, [P, c.c_char_p, i64]),
         "dissem_get_option": (c.c_int, [P, c.c_char_p, c.POINTER(i64)]),
     }
@@ -111,6 +112,19 @@ def make_xfers(xfers: Iterable) -> "ctypes.Array[Xfer]":
         else:
             arr[i] = Xfer(x.src, x.dst, x.layer, 0, x.off, x.size, x.total)
     return arr
+
+
+NOALLOC_MAX_CHUNKS = 8192
+
+
+def checksum_noalloc(device: int, device_ptr: int, size: int, stream: Optional[int] = None) -> np.ndarray:
+    """dissem_checksum_noalloc: per-chunk (A, B) of a device buffer the caller owns, computed without any
+    device allocation (for hosts whose HBM is fully committed to their own pool, or that cannot tolerate
+    cudaMalloc's stalls).  One call at a time per GPU; at most 2 GiB."""
+    n = (size + CHUNK_BYTES - 1) // CHUNK_BYTES
+    out = np.zeros((n, 2), dtype=np.uint64)
+    _check(lib().dissem_checksum_noalloc(device, device_ptr, size, out.ctypes.data, n, stream))
+    return out
 
 
 class Engine:

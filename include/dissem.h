@@ -140,6 +140,28 @@ int dissem_layer_verify(dissem_ctx *ctx, int node, int layer, uint64_t *out, int
  * layerSrc.DataSize, node.go:1542; the ack condition is received == total, node.go:1555). */
 int dissem_layer_received(dissem_ctx *ctx, int node, int layer, int64_t *bytes_out);
 
+/* ---- for callers that cannot allocate device memory (no counterpart in the reference) ----------------- */
+/* Same per-chunk checksum pass as dissem_layer_verify, over any 16-byte-aligned device buffer the caller
+ * already owns, WITHOUT allocating or freeing anything: no cudaMalloc, no cudaFree, no pooled allocator.
+ * It exists for hosts where an allocation at this point is not an option — a serving process that has given
+ * all remaining HBM to its own pool (cudaMalloc would fail or fragment it), or a latency-critical caller for
+ * whom cudaMalloc/cudaFree's driver locks and device-wide wait would stall every other stream.
+ * The kernel's scratch (work-unit counters, one descriptor, the table it accumulates into) lives in a fixed
+ * array inside the library image, about 129 KiB of HBM on each GPU that runs this library, held until the
+ * process exits.  Limits and rules:
+ *   - at most DISSEM_NOALLOC_MAX_CHUNKS chunks per call (2 GiB); larger sizes fail with DISSEM_ERANGE;
+ *   - all calls on a GPU share the one array; each call clears the part it uses first, so results do not depend
+ *     on earlier calls, but two calls whose GPU work may overlap (other streams or threads) corrupt each other:
+ *     run them one after another;
+ *   - the first call on each GPU resolves the array's device address; make that first call at start-up, before
+ *     any stream capture begins on that GPU.
+ * device: CUDA ordinal that owns `data`.  data: device pointer, size bytes.  out: HOST array of 2*n_chunks
+ * u64 (A_c, B_c), n_chunks = ceil(size / DISSEM_CHUNK_BYTES).  stream: a cudaStream_t, or NULL for the default
+ * stream; the call returns after the stream has finished this work, with `out` filled. */
+#define DISSEM_NOALLOC_MAX_CHUNKS 8192
+int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t *out, int64_t n_chunks,
+                            void *stream);
+
 /* ---- tuning / introspection -------------------------------------------------------------------------- */
 /* key: "ctas_per_sm" (0 = occupancy-derived), "variant" (0 = register path, 1 = TMA bulk-staged path),
  * "reg_cfg" (register-path shape, threads x 16-byte loads in flight: 0 256x4, 1 512x4 (default), 2 256x8,
