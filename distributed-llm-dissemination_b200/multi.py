@@ -1,0 +1,63 @@
+"""One process per GPU: which rank owns which reference node, which transfers a rank launches, and which
+destination buffers it must map from its peers.  Pure host logic plus a torch.distributed all-gather of 64-byte
+handles (plumbing); the bytes themselves only ever move through the push kernels.
+
+Sharding follows SURVEY §8(e): the units are independent (dest, layer) transfers, each executed by the rank that
+owns the SOURCE node (push model); there is no data-path collective."""
+from __future__ import annotations
+
+from typing import Callable, Dict, Iterable, List, Sequence, Tuple
+
+
+def owner_round_robin(world: int) -> Callable[[int], int]:
+    """node i -> rank i % world (at world == number of nodes every node is its own GPU, as in the north star)."""
+    return lambda node: node % world
+
+
+def device_of_node(n_nodes: int, owner: Callable[[int], int], rank: int, local_device: int) -> List[int]:
+    """Argument for dissem_init: the local CUDA ordinal for nodes this rank owns, -1 for the others."""
+    return [local_device if owner(n) == rank else -1 for n in range(n_nodes)]
+
+
+def my_transfers(xfers: Sequence, owner: Callable[[int], int], rank: int) -> List:
+    """Transfers this rank launches: those whose source node it owns."""
+    return [x for x in xfers if owner(x.src_node) == rank]
+
+
+def exports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int) -> List[Tuple[int, int, int]]:
+    """(node, layer, total) of destination buffers this rank owns that some OTHER rank pushes into."""
+    out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.dst_node) == rank and owner(x.src_node) != rank}
+    return sorted(out)
+
+
+def imports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int) -> List[Tuple[int, int, int]]:
+    """(node, layer, total) of remote destination buffers this rank pushes into."""
+    out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.src_node) == rank and owner(x.dst_node) != rank}
+    return sorted(out)
+
+
+def exchange_handles(dist, world: int, rank: int, mine: Dict[Tuple[int, int], bytes]) -> Dict[Tuple[int, int], bytes]:
+    """All-gather {(node, layer): 64-byte handle}.  In the reference's terms the handle rides in the announceMsg
+    (message.go:31-41) that every node sends before distribution starts."""
+    everyone = [None] * world
+    dist.all_gather_object(everyone, {f"{n}:{l}": h for (n, l), h in mine.items()})
+    merged: Dict[Tuple[int, int], bytes] = {}
+    for r, items in enumerate(everyone):
+        for key, h in items.items():
+            n, l = key.split(":")
+            merged[(int(n), int(l))] = h
+    return merged
+
+
+def link_bytes(xfers: Iterable, owner: Callable[[int], int], world: int):
+    """Per-rank egress / ingress bytes that cross GPUs, and bytes that stay local: the inputs of the NVLink roofline
+    T* = max over GPUs of max(egress, ingress) / link bandwidth."""
+    egress, ingress, local = [0] * world, [0] * world, [0] * world
+    for x in xfers:
+        s, d = owner(x.src_node), owner(x.dst_node)
+        if s == d:
+            local[s] += x.size
+        else:
+            egress[s] += x.size
+            ingress[d] += x.size
+    return egress, ingress, local

@@ -295,3 +295,33 @@ def test_errors(eng):
         eng.send(0, 9, 1, 0, 100, 100)          # no such node
     with pytest.raises(d.DissemError):
         eng.wait(12345)
+
+
+# ---- two GPUs in one process (peer access): the same kernel pushing over NVLink ------------------------------
+def _n_gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+def test_peer_push_between_two_gpus():
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    size = 7 * d.CHUNK_BYTES + 999
+    with d.Engine([0, 1]) as eng:
+        eng.alloc(0, 4, size)
+        eng.fill(0, 4, d.FILL_PATTERN, SEED)
+        eng.alloc(1, 4, size)
+        eng.fill(1, 4, d.FILL_POISON)
+        eng.alloc(1, 5, size)
+        eng.fill(1, 5, d.FILL_PATTERN, SEED)
+        eng.alloc(0, 5, size)
+        eng.fill(0, 5, d.FILL_POISON)
+        # both directions in one submit: one launch per source GPU; fragments at odd offsets included
+        xs = [(0, 1, 4, 0, 100_003, size), (0, 1, 4, 100_003, size - 100_003, size), (1, 0, 5, 0, size, size)]
+        eng.wait(eng.submit(xs))
+        for (node, layer) in ((1, 4), (0, 5)):
+            want = o.fill_bytes(o.FILL_PATTERN, layer, size, SEED)
+            assert np.array_equal(eng.read(node, layer), want)
+            assert np.array_equal(eng.checksums(node, layer), o.checksum(want))
+            assert np.array_equal(eng.verify(node, layer), o.checksum(want))
+            assert eng.received(node, layer) == size

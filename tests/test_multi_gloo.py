@@ -1,0 +1,73 @@
+"""The N>1 host logic on CPU: two gloo ranks shard a plan, exchange (fake) buffer handles and agree on who pushes
+what.  No GPU, no compute entry point."""
+import importlib
+import os
+import socket
+import sys
+
+import pytest
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import dissem_b200 as d
+from oracle import dissem_oracle as o
+
+multi = importlib.import_module("distributed-llm-dissemination_b200.multi")
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, text, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        xfers = d.parse_plan(d.plan(text, 1, seed=5))
+        owner = multi.owner_round_robin(world)
+        mine = multi.my_transfers(xfers, owner, rank)
+        exp = multi.exports_needed(xfers, owner, rank)
+        imp = multi.imports_needed(xfers, owner, rank)
+        handles = {(n, l): bytes([rank]) * 32 + n.to_bytes(16, "little") + l.to_bytes(16, "little") for (n, l, _t) in exp}
+        merged = multi.exchange_handles(dist, world, rank, handles)
+        ok = all((n, l) in merged and merged[(n, l)][0] == owner(n) and
+                 int.from_bytes(merged[(n, l)][32:48], "little") == n for (n, l, _t) in imp)
+        dev = multi.device_of_node(8, owner, rank, 0)
+        q.put((rank, [(x.src_node, x.dst_node, x.layer) for x in mine], len(exp), len(imp), ok, dev))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_shard_the_plan_and_exchange_handles():
+    world = 2
+    text = o.config_stage_ring(8, 32, 1 << 20)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, text, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    full = d.parse_plan(d.plan(text, 1, seed=5))
+    union = sorted(t for (_r, mine, *_rest) in got for t in mine)
+    assert union == sorted((x.src_node, x.dst_node, x.layer) for x in full)          # every transfer launched exactly once
+    assert all(ok for (_r, _m, _e, _i, ok, _d) in got)
+    assert sum(e for (_r, _m, e, _i, _ok, _d) in got) == sum(i for (_r, _m, _e, i, _ok, _d) in got)
+    assert got[0][5] == [0, -1, 0, -1, 0, -1, 0, -1] and got[1][5] == [-1, 0, -1, 0, -1, 0, -1, 0]
+
+
+def test_link_bytes_roofline_inputs():
+    text = o.config_stage_ring(8, 32, o.S2)
+    xf = d.parse_plan(d.plan(text, 1, policy=1))                                     # balanced owners
+    eg, ing, loc = multi.link_bytes(xf, multi.owner_round_robin(8), 8)
+    assert sum(eg) == sum(ing) == 28 * o.S2 and sum(loc) == 0
+    assert max(ing) == 4 * o.S2                                                      # each receiver takes its stage
+    eg1, ing1, loc1 = multi.link_bytes(xf, multi.owner_round_robin(1), 1)
+    assert eg1 == [0] and loc1 == [28 * o.S2]
