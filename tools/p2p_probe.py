@@ -26,16 +26,6 @@ def main():
         print(json.dumps({"error": "needs 2 GPUs"}))
         return
     nodes = list(range(min(ngpu, 8)))
-    eng = d.Engine(nodes)                      # node i on device i
-    for n in nodes:
-        for l in range(NL):
-            eng.alloc(n, l, SIZE)
-            eng.fill(n, l, d.FILL_PATTERN, n)
-            eng.alloc(n, 100 + l, SIZE)        # landing buffers
-            eng.alloc(n, 200 + l, SIZE)
-    # landing buffers are addressed as the same layer id on the destination: emulate with distinct ids per direction
-    cases = {}
-    # one direction: node0 layers 0..NL-1 -> node1 (dest must hold the same layer id: use fresh engine ids)
     eng2 = d.Engine(nodes)
     for l in range(NL):
         eng2.alloc(0, l, SIZE); eng2.fill(0, l, d.FILL_PATTERN, 1)
@@ -85,7 +75,6 @@ def main():
         print(json.dumps({"case": "fan-in 1,2,3->0", "kernel_ms_best": best, "ingress_GBps_best": 12 * SIZE / best / 1e6}))
         eng3.close()
     eng2.close()
-    eng.close()
 
 
 if __name__ == "__main__":
