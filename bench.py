@@ -215,6 +215,8 @@ def run_ours(args, rank, world, local_rank):
     owner = multi.owner_round_robin(world)
     eng = d.Engine(multi.device_of_node(N_NODES, owner, rank, local_rank))
     eng.set_option("variant", args.variant)
+    eng.set_option("pull", args.pull)
+    pull = bool(args.pull)
     if args.reg_cfg is not None:
         eng.set_option("reg_cfg", args.reg_cfg)
     if args.ctas_per_sm is not None:
@@ -233,11 +235,11 @@ def run_ours(args, rank, world, local_rank):
             eng.fill(x.dst_node, x.layer, d.FILL_POISON)
     if dist is not None:
         # one process per GPU: ship the destination buffers' handles (the announce would carry them)
-        mine = {(n, l): eng.export(n, l) for (n, l, _t) in multi.exports_needed(xfers, owner, rank)}
+        mine = {(n, l): eng.export(n, l) for (n, l, _t) in multi.exports_needed(xfers, owner, rank, pull)}
         handles = multi.exchange_handles(dist, world, rank, mine)
-        for (n, l, total) in multi.imports_needed(xfers, owner, rank):
+        for (n, l, total) in multi.imports_needed(xfers, owner, rank, pull):
             eng.import_(n, l, total, handles[(n, l)])
-    my_xfers = multi.my_transfers(xfers, owner, rank)
+    my_xfers = multi.my_transfers(xfers, owner, rank, pull)
     my_bytes = sum(x.size for x in my_xfers)
     sched = eng.compile(xfers)
     units, launches_per_step, sched_bytes = eng.sched_info(sched)
@@ -281,7 +283,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- end to end through the C ABI with host buffers ---------------------------------------------------
     import ctypes
     L = d.lib()
-    src_pairs = sorted({(x.src_node, x.layer) for x in my_xfers})
+    src_pairs = sorted({(x.src_node, x.layer) for x in xfers if owner(x.src_node) == rank})
     pinned = {}
     for (node, layer) in src_pairs:
         p = ctypes.c_void_p()
@@ -297,6 +299,8 @@ def run_ours(args, rank, world, local_rank):
     def e2e_step():
         for (node, layer), p in pinned.items():
             eng.write(node, layer, None, ptr=p.value, size=LAYER_BYTES)
+        if pull and dist is not None:          # remote readers must not start before the upload has landed
+            barrier()
         pl = d.parse_plan(d.plan(text, MODE, seed=SEED, policy=0))
         t = eng.submit(pl)
         eng.wait(t)
@@ -381,7 +385,7 @@ def run_ours(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "delivered_bytes_per_step": D, "nodes_per_gpu": N_NODES // world if world <= 8 else 1,
                        "l2": "inputs (3.76 GB touched per step) far exceed the 126 MB L2; no flush needed",
-                       "kernel_variant": "tma" if args.variant == 1 else "register", "units_per_launch": units},
+                       "kernel_variant": "tma" if args.variant == 1 else "register", "mode": "pull" if args.pull else "push", "units_per_launch": units},
             "device_ms_per_step": dev_step_s * 1e3,
             "completion_time_ms": step_s * 1e3,
             "e2e": None if args.no_e2e else {"value": D / e2e_step_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
@@ -411,6 +415,7 @@ def main():
     ap.add_argument("--variant", type=int, default=0, help="0 register path, 1 TMA bulk-staged path")
     ap.add_argument("--reg-cfg", type=int, default=None)
     ap.add_argument("--ctas-per-sm", type=int, default=None)
+    ap.add_argument("--pull", type=int, default=0, help="1: the destination GPU pulls instead of the source pushing")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the end-to-end leg")
     args = ap.parse_args()

@@ -100,7 +100,7 @@ struct dissem_ctx {
     std::map<int64_t, Ticket> tickets;
     int64_t next_id = 1;
     // options
-    int64_t opt_ctas_per_sm = 0, opt_variant = 0, opt_unit_bytes = 0, opt_reg_cfg = 1;
+    int64_t opt_ctas_per_sm = 0, opt_variant = 0, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0;
 };
 
 namespace dissem {
@@ -172,8 +172,10 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         if (x.size < 0 || x.off < 0 || x.off + x.size > x.total)
             return set_error(DISSEM_ERANGE, "transfer %d: [%lld,+%lld) outside layer of %lld bytes", i,
                              (long long)x.off, (long long)x.size, (long long)x.total);
-        int slot = ctx->node_dev_slot[x.src_node];
-        if (slot < 0) continue;          // the owner process of src_node runs it
+        // push (default): the GPU that holds the source runs the transfer and stores into the destination;
+        // pull: the destination's GPU runs it and loads from the (possibly remote) source.
+        int slot = ctx->node_dev_slot[ctx->opt_pull ? x.dst_node : x.src_node];
+        if (slot < 0) continue;          // the process that owns the executing side runs it
         if (x.size == 0) continue;       // an empty layerMsg moves nothing (LayerSize 0)
         by_dev[slot].push_back(x);
     }
@@ -768,6 +770,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     std::string k(key);
     if (k == "ctas_per_sm") { if (value < 0 || value > 32) return set_error(DISSEM_EINVAL, "ctas_per_sm out of range"); ctx->opt_ctas_per_sm = value; }
     else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
+    else if (k == "pull") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "pull must be 0 or 1"); ctx->opt_pull = value; }
     else if (k == "reg_cfg") { if (value < 0 || value > 6) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..6"); ctx->opt_reg_cfg = value; }
     else if (k == "unit_bytes") {
         if (value != 0 && (value < 4096 || value > DISSEM_CHUNK_BYTES || (value & (value - 1)))) return set_error(DISSEM_EINVAL, "unit_bytes must be 0 or a power of two in [4096, 262144]");
@@ -783,6 +786,7 @@ int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out) {
     if (k == "ctas_per_sm") *value_out = ctx->opt_ctas_per_sm;
     else if (k == "variant") *value_out = ctx->opt_variant;
     else if (k == "reg_cfg") *value_out = ctx->opt_reg_cfg;
+    else if (k == "pull") *value_out = ctx->opt_pull;
     else if (k == "unit_bytes") *value_out = ctx->opt_unit_bytes;
     else return set_error(DISSEM_EINVAL, "unknown option '%s'", key);
     return DISSEM_OK;

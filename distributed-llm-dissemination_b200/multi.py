@@ -19,20 +19,27 @@ def device_of_node(n_nodes: int, owner: Callable[[int], int], rank: int, local_d
     return [local_device if owner(n) == rank else -1 for n in range(n_nodes)]
 
 
-def my_transfers(xfers: Sequence, owner: Callable[[int], int], rank: int) -> List:
-    """Transfers this rank launches: those whose source node it owns."""
-    return [x for x in xfers if owner(x.src_node) == rank]
+def my_transfers(xfers: Sequence, owner: Callable[[int], int], rank: int, pull: bool = False) -> List:
+    """Transfers this rank launches: those whose source node it owns (push) or whose destination it owns (pull)."""
+    return [x for x in xfers if owner(x.dst_node if pull else x.src_node) == rank]
 
 
-def exports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int) -> List[Tuple[int, int, int]]:
-    """(node, layer, total) of destination buffers this rank owns that some OTHER rank pushes into."""
-    out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.dst_node) == rank and owner(x.src_node) != rank}
+def exports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int, pull: bool = False) -> List[Tuple[int, int, int]]:
+    """(node, layer, total) of buffers this rank owns that some OTHER rank touches: destination buffers it is
+    pushed into, or (pull) source layers that are read from it."""
+    if pull:
+        out = {(x.src_node, x.layer, x.total) for x in xfers if owner(x.src_node) == rank and owner(x.dst_node) != rank}
+    else:
+        out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.dst_node) == rank and owner(x.src_node) != rank}
     return sorted(out)
 
 
-def imports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int) -> List[Tuple[int, int, int]]:
-    """(node, layer, total) of remote destination buffers this rank pushes into."""
-    out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.src_node) == rank and owner(x.dst_node) != rank}
+def imports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int, pull: bool = False) -> List[Tuple[int, int, int]]:
+    """(node, layer, total) of remote buffers this rank's kernels touch."""
+    if pull:
+        out = {(x.src_node, x.layer, x.total) for x in xfers if owner(x.dst_node) == rank and owner(x.src_node) != rank}
+    else:
+        out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.src_node) == rank and owner(x.dst_node) != rank}
     return sorted(out)
 
 

@@ -166,7 +166,9 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
 /* key: "ctas_per_sm" (0 = occupancy-derived), "variant" (0 = register path, 1 = TMA bulk-staged path),
  * "reg_cfg" (register-path shape, threads x 16-byte loads in flight: 0 256x4, 1 512x4 (default), 2 256x8,
  * 3 512x8, 4 1024x4, 5 1024x2, 6 512x2),
- * "unit_bytes" (0 = auto; else power of two in [4096, 262144]). */
+ * "unit_bytes" (0 = auto; else power of two in [4096, 262144]),
+ * "pull" (0 = the source's GPU pushes (default); 1 = the destination's GPU pulls: then a process executes the
+ *  transfers whose DESTINATION node is local and needs the remote SOURCE layers imported). */
 int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value);
 int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out);
 

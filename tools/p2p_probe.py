@@ -35,16 +35,20 @@ def main():
     uni = [(0, 1, l, 0, SIZE, SIZE) for l in range(NL)]
     bidi = uni + [(1, 0, 50 + l, 0, SIZE, SIZE) for l in range(NL)]
     for name, xs in (("0->1", uni), ("0<->1", bidi)):
-        for ctas in (0, 1, 2, 4):
+        for variant, pull, ctas, cfg in ((0, 0, 0, 1), (0, 0, 1, 1), (0, 1, 0, 1), (0, 1, 0, 3), (0, 1, 1, 1),
+                                         (1, 0, 0, 1), (1, 0, 1, 1), (1, 1, 0, 1)):
+            eng2.set_option("variant", variant)
+            eng2.set_option("pull", pull)
             eng2.set_option("ctas_per_sm", ctas)
-            for cfg in (1, 3):
-                eng2.set_option("reg_cfg", cfg)
-                s = eng2.compile(xs)
-                best, avg = timed(eng2, s)
-                per_dir = NL * SIZE
-                print(json.dumps({"case": name, "ctas_per_sm": ctas, "reg_cfg": cfg, "kernel_ms_best": best, "kernel_ms_avg": avg,
-                                  "GBps_per_direction_best": per_dir / best / 1e6, "GBps_per_direction_avg": per_dir / avg / 1e6}))
-                eng2.sched_free(s)
+            eng2.set_option("reg_cfg", cfg)
+            s = eng2.compile(xs)
+            best, avg = timed(eng2, s)
+            per_dir = NL * SIZE
+            print(json.dumps({"case": name, "variant": "tma" if variant else "reg", "mode": "pull" if pull else "push",
+                              "ctas_per_sm": ctas, "reg_cfg": cfg, "kernel_ms_best": best, "kernel_ms_avg": avg,
+                              "GBps_per_direction_best": per_dir / best / 1e6, "GBps_per_direction_avg": per_dir / avg / 1e6}), flush=True)
+            eng2.sched_free(s)
+    eng2.set_option("variant", 0); eng2.set_option("pull", 0); eng2.set_option("ctas_per_sm", 0); eng2.set_option("reg_cfg", 1)
     # verify one landing buffer
     ok = bool((eng2.verify(1, 0) == eng2.verify(0, 0)).all() and (eng2.checksums(1, 0) == eng2.verify(0, 0)).all())
     print(json.dumps({"verified": ok, "received": eng2.received(1, 0)}))
