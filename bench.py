@@ -217,6 +217,8 @@ def run_ours(args, rank, world, local_rank):
     eng.set_option("variant", args.variant)
     eng.set_option("pull", args.pull)
     pull = bool(args.pull)
+    if args.tma_cfg is not None:
+        eng.set_option("tma_cfg", args.tma_cfg)
     if args.reg_cfg is not None:
         eng.set_option("reg_cfg", args.reg_cfg)
     if args.ctas_per_sm is not None:
@@ -412,8 +414,9 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--variant", type=int, default=0, help="0 register path, 1 TMA bulk-staged path")
+    ap.add_argument("--variant", type=int, default=1, help="0 register path, 1 TMA bulk-staged path")
     ap.add_argument("--reg-cfg", type=int, default=None)
+    ap.add_argument("--tma-cfg", type=int, default=None)
     ap.add_argument("--ctas-per-sm", type=int, default=None)
     ap.add_argument("--pull", type=int, default=0, help="1: the destination GPU pulls instead of the source pushing")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -100,7 +100,7 @@ struct dissem_ctx {
     std::map<int64_t, Ticket> tickets;
     int64_t next_id = 1;
     // options
-    int64_t opt_ctas_per_sm = 0, opt_variant = 0, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0;
+    int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0;
 };
 
 namespace dissem {
@@ -240,7 +240,7 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
         CUDA_TRY(cudaEventRecord(tp.start, ds.stream));
         CUDA_TRY(launch_zero_csum(p.d_descs, p.n_descs, ds.stream));
         CUDA_TRY(cudaEventRecord(tp.mid, ds.stream));
-        LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg};
+        LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
         CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
         CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
     }
@@ -753,7 +753,7 @@ int dissem_layer_verify(dissem_ctx *ctx, int node, int layer, uint64_t *out, int
     cudaError_t e = cudaMemsetAsync(scratch, 0, 256 + table_bytes, ds->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(scratch, &d, sizeof d, cudaMemcpyHostToDevice, ds->stream);
     if (e == cudaSuccess) {
-        LaunchCfg cfg{ds->n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg};
+        LaunchCfg cfg{ds->n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
         e = launch_copy_csum(reinterpret_cast<XferDesc *>(scratch), 1, units_of(0, lb->size, kChunkShift), kChunkShift,
                              ds->counters, cfg, ds->stream, nullptr);
     }
@@ -770,6 +770,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     std::string k(key);
     if (k == "ctas_per_sm") { if (value < 0 || value > 32) return set_error(DISSEM_EINVAL, "ctas_per_sm out of range"); ctx->opt_ctas_per_sm = value; }
     else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
+    else if (k == "tma_cfg") { if (value < 0 || value > 5) return set_error(DISSEM_EINVAL, "tma_cfg must be 0..5"); ctx->opt_tma_cfg = value; }
     else if (k == "pull") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "pull must be 0 or 1"); ctx->opt_pull = value; }
     else if (k == "reg_cfg") { if (value < 0 || value > 6) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..6"); ctx->opt_reg_cfg = value; }
     else if (k == "unit_bytes") {
@@ -787,6 +788,7 @@ int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out) {
     else if (k == "variant") *value_out = ctx->opt_variant;
     else if (k == "reg_cfg") *value_out = ctx->opt_reg_cfg;
     else if (k == "pull") *value_out = ctx->opt_pull;
+    else if (k == "tma_cfg") *value_out = ctx->opt_tma_cfg;
     else if (k == "unit_bytes") *value_out = ctx->opt_unit_bytes;
     else return set_error(DISSEM_EINVAL, "unknown option '%s'", key);
     return DISSEM_OK;

@@ -44,6 +44,7 @@ struct LaunchCfg {
     int ctas_per_sm;   // 0 = use the occupancy calculator
     int variant;       // 0 register path, 1 TMA bulk-staged path
     int reg_cfg;       // register-path shape (threads x loads in flight): 0 256x4, 1 512x4 (default), 2 256x8, 3 512x8, 4 1024x4, 5 1024x2, 6 512x2
+    int tma_cfg = 0;   // TMA ring shape (stage bytes x stages, store lag): 0 16Kx6/3 (default), 1 32Kx3/1, 2 8Kx12/6, 3 16Kx4/2, 4 8Kx6/3, 5 4Kx12/6
 };
 
 // Zero the checksum entries of every chunk a descriptor covers completely (so that launching the same

@@ -14,9 +14,8 @@ namespace dissem {
 
 namespace {
 
-constexpr int kStageBytes = 16384;
-constexpr int kStages = 6;
-constexpr int kStoreLag = 3;                 // bulk-store groups allowed in flight before a stage is retired
+// Ring shape is a template parameter: kStageBytes per bulk copy, kStages slots, kStoreLag bulk-store groups allowed in
+// flight before a stage is retired (needs kStoreLag + 2 <= kStages).
 constexpr int kConsumerWarps = 4;
 constexpr int kThreadsTma = 64 + 32 * kConsumerWarps;
 
@@ -35,6 +34,7 @@ struct StageMeta {
     int pad;
 };
 
+template <int kStageBytes, int kStages>
 struct __align__(128) SmemLayout {
     unsigned char data[kStages][kStageBytes];
     StageMeta meta[kStages];
@@ -112,11 +112,14 @@ __device__ __forceinline__ int find_desc_tma(const XferDesc *__restrict__ descs,
     return lo;
 }
 
+template <int kStageBytes, int kStages, int kStoreLag>
 __global__ void __launch_bounds__(kThreadsTma, 1)
 copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long total_units, int unit_shift,
                      SchedCounters *counters) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    SmemLayout &sm = *reinterpret_cast<SmemLayout *>(smem_raw);
+    static_assert(kStoreLag + 2 <= kStages, "ring too shallow for the store lag");
+    using Smem = SmemLayout<kStageBytes, kStages>;
+    Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
@@ -310,17 +313,18 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
     }
 }
 
-}  // namespace
-
-cudaError_t launch_copy_csum_tma(const XferDesc *descs, int n_descs, long long total_units, int unit_shift,
-                                 SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream, int *grid_out) {
-    static_assert(sizeof(SmemLayout) <= 110 * 1024, "two CTAs per SM");
-    const int smem = (int)sizeof(SmemLayout) + 128;
-    cudaError_t e = cudaFuncSetAttribute(copy_csum_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+template <int kStageBytes, int kStages, int kStoreLag>
+static cudaError_t launch_tma(const XferDesc *descs, int n_descs, long long total_units, int unit_shift,
+                              SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream, int *grid_out) {
+    using Smem = SmemLayout<kStageBytes, kStages>;
+    static_assert(sizeof(Smem) <= 112 * 1024, "two CTAs per SM");
+    auto kern = copy_csum_tma_kernel<kStageBytes, kStages, kStoreLag>;
+    const int smem = (int)sizeof(Smem) + 128;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     int per_sm = cfg.ctas_per_sm;
     if (per_sm <= 0) {
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, copy_csum_tma_kernel, kThreadsTma, smem);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreadsTma, smem);
         if (e != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
     }
@@ -328,8 +332,22 @@ cudaError_t launch_copy_csum_tma(const XferDesc *descs, int n_descs, long long t
     if (grid > total_units) grid = total_units;
     if (grid < 1) grid = 1;
     if (grid_out) *grid_out = (int)grid;
-    copy_csum_tma_kernel<<<(int)grid, kThreadsTma, smem, stream>>>(descs, n_descs, total_units, unit_shift, counters);
+    kern<<<(int)grid, kThreadsTma, smem, stream>>>(descs, n_descs, total_units, unit_shift, counters);
     return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_copy_csum_tma(const XferDesc *descs, int n_descs, long long total_units, int unit_shift,
+                                 SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream, int *grid_out) {
+    switch (cfg.tma_cfg) {
+        case 1: return launch_tma<32768, 3, 1>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 2: return launch_tma<8192, 12, 6>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 3: return launch_tma<16384, 4, 2>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 4: return launch_tma<8192, 6, 3>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 5: return launch_tma<4096, 12, 6>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        default: return launch_tma<16384, 6, 3>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+    }
 }
 
 }  // namespace dissem
