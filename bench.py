@@ -215,8 +215,11 @@ def run_ours(args, rank, world, local_rank):
     owner = multi.owner_round_robin(world)
     eng = d.Engine(multi.device_of_node(N_NODES, owner, rank, local_rank))
     eng.set_option("variant", args.variant)
-    eng.set_option("pull", args.pull)
-    pull = bool(args.pull)
+    eng.set_option("pull", 1 if args.pull == 1 else 0)
+    pull = args.pull == 1
+    if args.pull == 2:
+        xfers = d.plan_directions(xfers, [owner(n) for n in range(N_NODES)])
+    n_pulled = sum(1 for x in xfers if pull or (x.flags & 1))
     if args.tma_cfg is not None:
         eng.set_option("tma_cfg", args.tma_cfg)
     if args.reg_cfg is not None:
@@ -301,9 +304,11 @@ def run_ours(args, rank, world, local_rank):
     def e2e_step():
         for (node, layer), p in pinned.items():
             eng.write(node, layer, None, ptr=p.value, size=LAYER_BYTES)
-        if pull and dist is not None:          # remote readers must not start before the upload has landed
+        if n_pulled and dist is not None:      # remote readers must not start before the upload has landed
             barrier()
         pl = d.parse_plan(d.plan(text, MODE, seed=SEED, policy=0))
+        if args.pull == 2:
+            pl = d.plan_directions(pl, [owner(n) for n in range(N_NODES)])
         t = eng.submit(pl)
         eng.wait(t)
         return [eng.checksums(n, l) for (n, l) in my_dsts]
@@ -387,7 +392,7 @@ def run_ours(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "delivered_bytes_per_step": D, "nodes_per_gpu": N_NODES // world if world <= 8 else 1,
                        "l2": "inputs (3.76 GB touched per step) far exceed the 126 MB L2; no flush needed",
-                       "kernel_variant": "tma" if args.variant == 1 else "register", "mode": "pull" if args.pull else "push", "units_per_launch": units},
+                       "kernel_variant": "tma" if args.variant == 1 else "register", "mode": {0: "push", 1: "pull", 2: "auto"}[args.pull], "transfers_pulled": n_pulled, "units_per_launch": units},
             "device_ms_per_step": dev_step_s * 1e3,
             "completion_time_ms": step_s * 1e3,
             "e2e": None if args.no_e2e else {"value": D / e2e_step_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
@@ -418,7 +423,8 @@ def main():
     ap.add_argument("--reg-cfg", type=int, default=None)
     ap.add_argument("--tma-cfg", type=int, default=None)
     ap.add_argument("--ctas-per-sm", type=int, default=None)
-    ap.add_argument("--pull", type=int, default=0, help="1: the destination GPU pulls instead of the source pushing")
+    ap.add_argument("--pull", type=int, default=2, help="0 push everything, 1 pull everything, 2 per-transfer choice "
+                    "by dissem_plan_directions (default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the end-to-end leg")
     args = ap.parse_args()

@@ -72,6 +72,7 @@ def load_library() -> ctypes.CDLL:
         "dissem_schedule_launch": (c.c_int, [P, i64, c.POINTER(i64)]),
         "dissem_schedule_free": (c.c_int, [P, i64]),
         "dissem_schedule_info": (c.c_int, [P, i64, c.POINTER(i64), c.POINTER(c.c_int), c.POINTER(i64)]),
+        "dissem_plan_directions": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int]),
         "dissem_wait": (c.c_int, [P, i64, c.POINTER(c.c_double)]),
         "dissem_wait_detail": (c.c_int, [P, i64, c.POINTER(c.c_double), c.POINTER(c.c_double)]),
         "dissem_poll": (c.c_int, [P, i64, c.POINTER(c.c_int)]),
@@ -110,8 +111,20 @@ def make_xfers(xfers: Iterable) -> "ctypes.Array[Xfer]":
             s, d, l, off, size, total = x
             arr[i] = Xfer(s, d, l, 0, off, size, total)
         else:
-            arr[i] = Xfer(x.src, x.dst, x.layer, 0, x.off, x.size, x.total)
+            arr[i] = Xfer(x.src, x.dst, x.layer, getattr(x, "flags", 0), x.off, x.size, x.total)
     return arr
+
+
+XFER_PULL = 1
+
+
+def plan_directions(xfers: List["Xfer"], gpu_of_node: Sequence[int]) -> List["Xfer"]:
+    """dissem_plan_directions: set DISSEM_XFER_PULL on the transfers that are better pulled by their destination
+    GPU (reverse NVLink direction idle), clear it on the others.  Returns new Xfer structs."""
+    arr = make_xfers(xfers)
+    g = (ctypes.c_int * len(gpu_of_node))(*gpu_of_node)
+    _check(lib().dissem_plan_directions(arr, len(xfers), g, len(gpu_of_node)))
+    return [Xfer(a.src_node, a.dst_node, a.layer, a.flags, a.off, a.size, a.total) for a in arr[:len(xfers)]]
 
 
 NOALLOC_MAX_CHUNKS = 8192

@@ -99,8 +99,12 @@ struct dissem_ctx {
     std::map<int64_t, Sched> scheds;
     std::map<int64_t, Ticket> tickets;
     int64_t next_id = 1;
+    // NVLS multicast objects, keyed by (layer, team of nodes: source first, then destinations ascending)
+    std::map<std::pair<int, std::vector<int>>, McObject> mcasts;
+    int64_t mcast_groups_compiled = 0;
+    std::string mcast_note;
     // options
-    int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0;
+    int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0, opt_alloc_vmm = 0, opt_mcast = 1;
 };
 
 namespace dissem {
@@ -160,6 +164,45 @@ static int pick_unit_shift(dissem_ctx *ctx, const std::vector<std::vector<dissem
     return shift;
 }
 
+// NVLS: one multicast object per (layer, source, destination set), over the layer buffers of the team's GPUs.
+// The source GPU must be a member to address the object, so its own copy of the layer is bound as well: the
+// multicast store rewrites the source's bytes with themselves (and bumps its own trailer, which nobody reads).
+// Returns NULL when the group cannot be multicast (capability or layout); the caller then sends unicast copies.
+static McObject *get_or_make_mcast(dissem_ctx *ctx, int layer, int src_node, const std::vector<int> &dst_nodes) {
+    std::vector<int> team{src_node};
+    std::vector<int> sorted_dsts(dst_nodes);
+    std::sort(sorted_dsts.begin(), sorted_dsts.end());
+    team.insert(team.end(), sorted_dsts.begin(), sorted_dsts.end());
+    auto key = std::make_pair(layer, team);
+    auto it = ctx->mcasts.find(key);
+    if (it != ctx->mcasts.end()) return it->second.valid() ? &it->second : nullptr;
+    McObject mc;                                   // cached even when invalid: do not retry a failing set-up per compile
+    std::vector<int> devices;
+    std::vector<const VmmBlock *> blocks;
+    bool ok = true;
+    for (int node : team) {
+        int slot = ctx->node_dev_slot[node];
+        auto li = ctx->layers[node].find(layer);
+        if (slot < 0 || li == ctx->layers[node].end() || !li->second.vmm) { ok = false; break; }
+        int dev = ctx->devs[slot].dev;
+        if (std::find(devices.begin(), devices.end(), dev) != devices.end()) { ok = false; break; }   // one block per GPU
+        devices.push_back(dev);
+        blocks.push_back(&li->second.blk);
+    }
+    std::string why;
+    if (ok && !mcast_supported(devices, &why)) ok = false;
+    if (ok) {
+        why = mcast_create(devices, blocks, &mc);
+        if (!why.empty()) ok = false;
+    }
+    if (!ok) {
+        ctx->mcast_note = why.empty() ? "group layout cannot be multicast (non-VMM layer, remote node or shared GPU)" : why;
+        mc = McObject();
+    }
+    auto ins = ctx->mcasts.emplace(key, mc);
+    return ins.first->second.valid() ? &ins.first->second : nullptr;
+}
+
 static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched *out) {
     if (n < 0 || (n > 0 && !xfers)) return set_error(DISSEM_EINVAL, "bad transfer list");
     std::vector<std::vector<dissem_xfer>> by_dev(ctx->devs.size());
@@ -174,7 +217,8 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                              (long long)x.off, (long long)x.size, (long long)x.total);
         // push (default): the GPU that holds the source runs the transfer and stores into the destination;
         // pull: the destination's GPU runs it and loads from the (possibly remote) source.
-        int slot = ctx->node_dev_slot[ctx->opt_pull ? x.dst_node : x.src_node];
+        const bool pull = ctx->opt_pull == 1 || (ctx->opt_pull == 0 && (x.flags & DISSEM_XFER_PULL));
+        int slot = ctx->node_dev_slot[pull ? x.dst_node : x.src_node];
         if (slot < 0) continue;          // the process that owns the executing side runs it
         if (x.size == 0) continue;       // an empty layerMsg moves nothing (LayerSize 0)
         by_dev[slot].push_back(x);
@@ -185,10 +229,56 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         std::vector<XferDesc> descs;
         long long units = 0;
         int64_t bytes = 0;
-        for (auto &x : by_dev[slot]) {
+        std::vector<dissem_xfer> &list = by_dev[slot];
+        std::vector<char> used(list.size(), 0);
+        auto is_pull = [&](const dissem_xfer &x) { return ctx->opt_pull == 1 || (ctx->opt_pull == 0 && (x.flags & DISSEM_XFER_PULL)); };
+        for (size_t i = 0; i < list.size(); ++i) {
+            if (used[i]) continue;
+            const dissem_xfer &x = list[i];
             LayerBuf *src = nullptr, *dst = nullptr;
             int rc = find_layer(ctx, x.src_node, x.layer, &src);
             if (rc) return rc;
+            // the same bytes of the same source for several destinations: one multicast store stream (K2)
+            std::vector<size_t> members{i};
+            if (ctx->opt_mcast && !is_pull(x) && x.off % 16 == 0 && x.size % 16 == 0)
+                for (size_t j = i + 1; j < list.size(); ++j) {
+                    const dissem_xfer &y = list[j];
+                    if (!used[j] && !is_pull(y) && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off &&
+                        y.size == x.size && y.total == x.total && y.dst_node != x.dst_node)
+                        members.push_back(j);
+                }
+            if (members.size() >= 2 || (ctx->opt_mcast == 2 && !is_pull(x) && x.off % 16 == 0 && x.size % 16 == 0 &&
+                                        ctx->node_dev_slot[x.dst_node] != ctx->node_dev_slot[x.src_node])) {
+                std::vector<int> dsts;
+                bool sizes_ok = src->size == x.total;
+                for (size_t m : members) {
+                    dsts.push_back(list[m].dst_node);
+                    LayerBuf *dl = nullptr;
+                    if (find_layer(ctx, list[m].dst_node, x.layer, &dl) || dl->size != x.total) sizes_ok = false;
+                }
+                McObject *mc = sizes_ok ? get_or_make_mcast(ctx, x.layer, x.src_node, dsts) : nullptr;
+                if (mc) {
+                    uint8_t *mbase = reinterpret_cast<uint8_t *>(mc->va);
+                    XferDesc d;
+                    memset(&d, 0, sizeof d);
+                    d.src = src->base;
+                    d.dst = mbase;
+                    d.csum = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off() + 256);
+                    d.received = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off());
+                    d.off = x.off;
+                    d.size = x.size;
+                    d.total = x.total;
+                    d.first_unit = units;
+                    d.flags = kFlagMulticast;
+                    units += units_of(x.off, x.size, out->unit_shift);
+                    bytes += x.size * (int64_t)members.size();
+                    descs.push_back(d);
+                    for (size_t m : members) used[m] = 1;
+                    ctx->mcast_groups_compiled++;
+                    continue;
+                }
+            }
+            used[i] = 1;
             rc = find_layer(ctx, x.dst_node, x.layer, &dst);
             if (rc) return rc;
             if (src->size != x.total || dst->size != x.total)
@@ -334,10 +424,13 @@ int dissem_close(dissem_ctx *ctx) {
         }
         for (auto &kv : ctx->tickets) drop_ticket(kv.second);
         for (auto &kv : ctx->scheds) free_sched(ctx, kv.second);
+        for (auto &kv : ctx->mcasts) mcast_destroy(&kv.second);
+        ctx->mcasts.clear();
         for (int n = 0; n < ctx->n_nodes; ++n)
             for (auto &kv : ctx->layers[n]) {
                 LayerBuf &lb = kv.second;
                 if (lb.imported) cudaIpcCloseMemHandle(lb.base);
+                else if (lb.vmm) vmm_free(&lb.blk);
                 else {
                     cudaSetDevice(lb.device);
                     cudaFree(lb.base);
@@ -367,14 +460,24 @@ int dissem_layer_alloc(dissem_ctx *ctx, int node, int layer, int64_t size) {
     lb.size = size;
     lb.device = ds->dev;
     CUDA_TRY(cudaSetDevice(ds->dev));
-    void *p = nullptr;
-    cudaError_t e = cudaMalloc(&p, (size_t)lb.alloc_bytes());
-    if (e == cudaErrorMemoryAllocation) {
-        cudaGetLastError();
-        return set_error(DISSEM_ENOMEM, "out of HBM allocating %lld bytes for layer %d on node %d", (long long)lb.alloc_bytes(), layer, node);
+    if (ctx->opt_alloc_vmm) {
+        // VMM-backed: can be bound to an NVLS multicast object; mapped for every local GPU (peer stores)
+        std::vector<int> access;
+        for (auto &d : ctx->devs) access.push_back(d.dev);
+        std::string err = vmm_alloc(ds->dev, access, (size_t)lb.alloc_bytes(), &lb.blk);
+        if (!err.empty()) return set_error(DISSEM_ECUDA, "VMM allocation of layer %d on node %d: %s", layer, node, err.c_str());
+        lb.vmm = true;
+        lb.base = reinterpret_cast<uint8_t *>(lb.blk.va);
+    } else {
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, (size_t)lb.alloc_bytes());
+        if (e == cudaErrorMemoryAllocation) {
+            cudaGetLastError();
+            return set_error(DISSEM_ENOMEM, "out of HBM allocating %lld bytes for layer %d on node %d", (long long)lb.alloc_bytes(), layer, node);
+        }
+        CUDA_TRY(e);
+        lb.base = static_cast<uint8_t *>(p);
     }
-    CUDA_TRY(e);
-    lb.base = static_cast<uint8_t *>(p);
     CUDA_TRY(cudaMemsetAsync(lb.base + lb.trailer_off(), 0, (size_t)lb.trailer_bytes(), ds->stream));
     ctx->layers[node][layer] = lb;
     return DISSEM_OK;
@@ -390,7 +493,16 @@ int dissem_layer_free(dissem_ctx *ctx, int node, int layer) {
         CUDA_TRY(cudaSetDevice(ds.dev));
         CUDA_TRY(cudaStreamSynchronize(ds.stream));
     }
+    // multicast objects that bind this buffer go first
+    for (auto it = ctx->mcasts.begin(); it != ctx->mcasts.end();) {
+        const std::vector<int> &team = it->first.second;
+        if (it->first.first == layer && std::find(team.begin(), team.end(), node) != team.end()) {
+            mcast_destroy(&it->second);
+            it = ctx->mcasts.erase(it);
+        } else ++it;
+    }
     if (lb->imported) CUDA_TRY(cudaIpcCloseMemHandle(lb->base));
+    else if (lb->vmm) vmm_free(&lb->blk);
     else {
         CUDA_TRY(cudaSetDevice(lb->device));
         CUDA_TRY(cudaFree(lb->base));
@@ -503,6 +615,7 @@ int dissem_layer_export(dissem_ctx *ctx, int node, int layer, uint8_t handle_out
     int rc = find_layer(ctx, node, layer, &lb);
     if (rc) return rc;
     if (lb->imported) return set_error(DISSEM_EINVAL, "layer %d of node %d is itself imported", layer, node);
+    if (lb->vmm) return set_error(DISSEM_ENOTSUP, "layer %d of node %d is VMM-backed (alloc_vmm); cross-process export of such layers is not implemented", layer, node);
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     cudaIpcMemHandle_t h;
     CUDA_TRY(cudaSetDevice(lb->device));
@@ -620,6 +733,30 @@ int dissem_send(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t 
     x.size = size;
     x.total = total;
     return dissem_schedule_submit(ctx, &x, 1, out);
+}
+
+int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, int n_nodes) {
+    if (n < 0 || (n > 0 && !xfers) || !gpu_of_node || n_nodes <= 0) return set_error(DISSEM_EINVAL, "dissem_plan_directions: bad arguments");
+    std::map<int, int64_t> egress, ingress;
+    for (int i = 0; i < n; ++i) {
+        const dissem_xfer &x = xfers[i];
+        if (x.src_node < 0 || x.src_node >= n_nodes || x.dst_node < 0 || x.dst_node >= n_nodes)
+            return set_error(DISSEM_ENOENT, "transfer %d names a node outside [0,%d)", i, n_nodes);
+        const int gs = gpu_of_node[x.src_node], gd = gpu_of_node[x.dst_node];
+        if (gs == gd) continue;
+        egress[gs] += x.size;
+        ingress[gd] += x.size;
+    }
+    for (int i = 0; i < n; ++i) {
+        dissem_xfer &x = xfers[i];
+        const int gs = gpu_of_node[x.src_node], gd = gpu_of_node[x.dst_node];
+        x.flags &= ~DISSEM_XFER_PULL;
+        if (gs == gd) continue;
+        const int64_t forward = std::max(egress[gs], ingress[gd]);
+        const int64_t reverse = std::max(ingress[gs], egress[gd]);
+        if (2 * reverse < forward) x.flags |= DISSEM_XFER_PULL;
+    }
+    return DISSEM_OK;
 }
 
 int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out) { return dissem_wait_detail(ctx, ticket, ms_out, nullptr); }
@@ -771,7 +908,9 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     if (k == "ctas_per_sm") { if (value < 0 || value > 32) return set_error(DISSEM_EINVAL, "ctas_per_sm out of range"); ctx->opt_ctas_per_sm = value; }
     else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
     else if (k == "tma_cfg") { if (value < 0 || value > 5) return set_error(DISSEM_EINVAL, "tma_cfg must be 0..5"); ctx->opt_tma_cfg = value; }
-    else if (k == "pull") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "pull must be 0 or 1"); ctx->opt_pull = value; }
+    else if (k == "alloc_vmm") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0 or 1"); ctx->opt_alloc_vmm = value; }
+    else if (k == "mcast") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "mcast must be 0, 1 or 2"); ctx->opt_mcast = value; }
+    else if (k == "pull") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "pull must be 0, 1 or 2"); ctx->opt_pull = value; }
     else if (k == "reg_cfg") { if (value < 0 || value > 6) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..6"); ctx->opt_reg_cfg = value; }
     else if (k == "unit_bytes") {
         if (value != 0 && (value < 4096 || value > DISSEM_CHUNK_BYTES || (value & (value - 1)))) return set_error(DISSEM_EINVAL, "unit_bytes must be 0 or a power of two in [4096, 262144]");
@@ -789,6 +928,16 @@ int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out) {
     else if (k == "reg_cfg") *value_out = ctx->opt_reg_cfg;
     else if (k == "pull") *value_out = ctx->opt_pull;
     else if (k == "tma_cfg") *value_out = ctx->opt_tma_cfg;
+    else if (k == "alloc_vmm") *value_out = ctx->opt_alloc_vmm;
+    else if (k == "mcast") *value_out = ctx->opt_mcast;
+    else if (k == "mcast_groups") *value_out = ctx->mcast_groups_compiled;     // read-only: multicast descriptors compiled so far
+    else if (k == "mcast_supported") {
+        std::vector<int> devs;
+        for (auto &d : ctx->devs) devs.push_back(d.dev);
+        std::string why;
+        *value_out = (devs.size() >= 2 && mcast_supported(devs, &why)) ? 1 : 0;
+        if (!*value_out) ctx->mcast_note = why;
+    }
     else if (k == "unit_bytes") *value_out = ctx->opt_unit_bytes;
     else return set_error(DISSEM_EINVAL, "unknown option '%s'", key);
     return DISSEM_OK;

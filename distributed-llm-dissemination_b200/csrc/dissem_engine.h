@@ -2,6 +2,8 @@
 #pragma once
 #include <stdint.h>
 
+#include "dissem_vmm.h"
+
 namespace dissem {
 
 int set_error(int code, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
@@ -14,6 +16,8 @@ struct LayerBuf {
     uint8_t *base = nullptr;
     int device = -1;        // CUDA ordinal of the owning device; -1 for an imported (remote) layer
     bool imported = false;
+    bool vmm = false;       // allocated through the VMM API (can be bound to an NVLS multicast object)
+    VmmBlock blk;
 
     int64_t n_chunks() const;
     int64_t trailer_off() const;

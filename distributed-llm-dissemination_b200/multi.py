@@ -19,27 +19,36 @@ def device_of_node(n_nodes: int, owner: Callable[[int], int], rank: int, local_d
     return [local_device if owner(n) == rank else -1 for n in range(n_nodes)]
 
 
+def _sides(x, pull):
+    """(executing node, other node) of a transfer: the source pushes unless the transfer is flagged PULL
+    (DISSEM_XFER_PULL, set by dissem_plan_directions) or `pull` forces it."""
+    is_pull = bool(pull) or bool(getattr(x, "flags", 0) & 1)
+    return (x.dst_node, x.src_node) if is_pull else (x.src_node, x.dst_node)
+
+
 def my_transfers(xfers: Sequence, owner: Callable[[int], int], rank: int, pull: bool = False) -> List:
-    """Transfers this rank launches: those whose source node it owns (push) or whose destination it owns (pull)."""
-    return [x for x in xfers if owner(x.dst_node if pull else x.src_node) == rank]
+    """Transfers this rank launches: those whose executing side it owns."""
+    return [x for x in xfers if owner(_sides(x, pull)[0]) == rank]
 
 
 def exports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int, pull: bool = False) -> List[Tuple[int, int, int]]:
-    """(node, layer, total) of buffers this rank owns that some OTHER rank touches: destination buffers it is
-    pushed into, or (pull) source layers that are read from it."""
-    if pull:
-        out = {(x.src_node, x.layer, x.total) for x in xfers if owner(x.src_node) == rank and owner(x.dst_node) != rank}
-    else:
-        out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.dst_node) == rank and owner(x.src_node) != rank}
+    """(node, layer, total) of buffers this rank owns that ANOTHER rank's kernel touches: destination buffers it
+    is pushed into, source layers that are pulled from it."""
+    out = set()
+    for x in xfers:
+        ex, other = _sides(x, pull)
+        if owner(other) == rank and owner(ex) != rank:
+            out.add((other, x.layer, x.total))
     return sorted(out)
 
 
 def imports_needed(xfers: Sequence, owner: Callable[[int], int], rank: int, pull: bool = False) -> List[Tuple[int, int, int]]:
     """(node, layer, total) of remote buffers this rank's kernels touch."""
-    if pull:
-        out = {(x.src_node, x.layer, x.total) for x in xfers if owner(x.dst_node) == rank and owner(x.src_node) != rank}
-    else:
-        out = {(x.dst_node, x.layer, x.total) for x in xfers if owner(x.src_node) == rank and owner(x.dst_node) != rank}
+    out = set()
+    for x in xfers:
+        ex, other = _sides(x, pull)
+        if owner(ex) == rank and owner(other) != rank:
+            out.add((other, x.layer, x.total))
     return sorted(out)
 
 

@@ -54,11 +54,15 @@ typedef int64_t dissem_sched;    /* one compiled schedule */
  * `layer` go from src_node's copy to the same offsets of dst_node's copy; total = full layer size
  * (LayerSize = size, TotalSize = total, Offert = off).  Modes 0/1 send whole layers (off = 0,
  * size = total; node.go:363, :1478); mode 3 sends fragments (node.go:1604-1606). */
+/* dissem_xfer.flags: who executes the transfer.  Default (0): the GPU holding the source pushes.  PULL: the
+ * destination's GPU loads from the source instead (its process needs the source layer imported). */
+#define DISSEM_XFER_PULL 1
+
 typedef struct dissem_xfer {
     int32_t src_node;
     int32_t dst_node;
     int32_t layer;
-    int32_t flags;   /* 0; reserved */
+    int32_t flags;   /* DISSEM_XFER_* */
     int64_t off;
     int64_t size;
     int64_t total;
@@ -122,6 +126,16 @@ int dissem_schedule_free(dissem_ctx *ctx, dissem_sched sched);
  * issues; bytes_out: bytes the local sources deliver. */
 int dissem_schedule_info(dissem_ctx *ctx, dissem_sched sched, int64_t *units_out, int *launches_out,
                          int64_t *bytes_out);
+/* Per-link transfer direction for a plan (no counterpart in the reference, which has one TCP direction).
+ * Measured on B200/NVLink 5 (profiles/): a PUSH stream carries ~710 GB/s whatever the reverse direction does;
+ * a PULL stream carries ~785 GB/s while the reverse direction of the same ports is idle but only ~640-675 GB/s
+ * when it is busy (read requests share it).  For each transfer this sets or clears DISSEM_XFER_PULL in place:
+ * pull when the data load on the reverse ports, max(ingress of the source GPU, egress of the destination GPU),
+ * is below half of the forward load max(egress of source, ingress of destination); transfers inside one GPU
+ * are left as pushes.  gpu_of_node[i]: any id of the GPU that holds node i (e.g. the rank).  Pure host logic;
+ * every process of a job computes the same answer from the same plan. */
+int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, int n_nodes);
+
 /* Block until the batch is complete (all bytes visible at their destinations).  ms_out (may be NULL):
  * device time of the batch, max over the source GPUs involved.  The ticket is consumed. */
 int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out);
@@ -167,9 +181,17 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
  * "reg_cfg" (register-path shape, threads x 16-byte loads in flight: 0 256x4, 1 512x4 (default), 2 256x8,
  * 3 512x8, 4 1024x4, 5 1024x2, 6 512x2),
  * "tma_cfg" (TMA ring shape, stage bytes x stages: 0 16Kx6 (default), 1 32Kx3, 2 8Kx12, 3 16Kx4, 4 8Kx6, 5 4Kx12),
+ * "alloc_vmm" (1 = dissem_layer_alloc uses the VMM API so that layers can be bound to NVLS multicast objects;
+ *  such layers cannot be exported to other processes yet),
+ * "mcast" (1 (default) = transfers of the same bytes from one source to several GPUs are sent as ONE NVLS
+ *  multicast store stream when every buffer involved is VMM-backed and local; 0 = always unicast fan-out;
+ *  2 = also route single-destination transfers to another GPU through a multicast object (a testing aid)),
+ * read-only: "mcast_supported" (do all local GPUs support multicast objects), "mcast_groups" (multicast
+ *  descriptors compiled so far),
  * "unit_bytes" (0 = auto; else power of two in [4096, 262144]),
- * "pull" (0 = the source's GPU pushes (default); 1 = the destination's GPU pulls: then a process executes the
- *  transfers whose DESTINATION node is local and needs the remote SOURCE layers imported). */
+ * "pull" (0 = follow each transfer's DISSEM_XFER_PULL flag (default); 1 = pull every transfer: a process then
+ *  executes the transfers whose DESTINATION node is local and needs the remote SOURCE layers imported;
+ *  2 = push every transfer whatever its flag). */
 int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value);
 int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out);
 

@@ -377,3 +377,59 @@ def test_variants_fragments_and_plan(variant, pull):
             w = o.fill_bytes(o.FILL_PATTERN, x.layer, lsize, SEED)
             assert np.array_equal(eng.read(x.dst_node, x.layer), w)
             assert np.array_equal(eng.checksums(x.dst_node, x.layer), o.checksum(w))
+
+
+def test_per_transfer_pull_flag_single_process():
+    """DISSEM_XFER_PULL on some transfers of a batch: same bytes, same tables (two GPUs when present)."""
+    two = _n_gpus() >= 2
+    size = 3 * d.CHUNK_BYTES + 77
+    with d.Engine([0, 1 if two else 0, 0]) as eng:
+        for l in range(4):
+            eng.alloc(0, l, size)
+            eng.fill(0, l, d.FILL_PATTERN, SEED)
+            eng.alloc(1, l, size)
+            eng.fill(1, l, d.FILL_POISON)
+        xs = [d.Xfer(0, 1, l, d.XFER_PULL if l % 2 else 0, 0, size, size) for l in range(4)]
+        eng.wait(eng.submit(xs))
+        for l in range(4):
+            want = o.fill_bytes(o.FILL_PATTERN, l, size, SEED)
+            assert np.array_equal(eng.read(1, l), want)
+            assert np.array_equal(eng.checksums(1, l), o.checksum(want))
+            assert eng.received(1, l) == size
+
+
+# ---- K2: NVLS multicast (one process, several GPUs) -------------------------------------------------------------
+def test_multicast_fanout_matches_unicast():
+    """A layer assigned to several GPUs goes out as ONE multimem.st stream; bytes, tables and counters at every
+    destination equal the oracle's.  With two GPUs the single remote destination is routed through a multicast
+    object too (mcast=2) so that the mechanism is still exercised."""
+    n = min(_n_gpus(), 8)
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    size = 9 * d.CHUNK_BYTES + 4096 + 16          # multiple of 16, ragged last chunk
+    with d.Engine(list(range(n))) as eng:
+        if not eng.get_option("mcast_supported"):
+            pytest.skip("this box has no multicast-object support")
+        eng.set_option("alloc_vmm", 1)
+        eng.set_option("mcast", 1 if n >= 3 else 2)
+        for layer in (0, 1):
+            eng.alloc(0, layer, size)
+            eng.fill(0, layer, d.FILL_PATTERN, SEED)
+            for dst in range(1, n):
+                eng.alloc(dst, layer, size)
+                eng.fill(dst, layer, d.FILL_POISON)
+        xs = [(0, dst, layer, 0, size, size) for layer in (0, 1) for dst in range(1, n)]
+        s = eng.compile(xs)
+        assert eng.get_option("mcast_groups") == 2, "the fan-out was not compiled to multicast"
+        for _ in range(2):
+            eng.wait(eng.launch(s))
+        for layer in (0, 1):
+            want = o.fill_bytes(o.FILL_PATTERN, layer, size, SEED)
+            cs = o.checksum(want)
+            assert np.array_equal(eng.read(0, layer), want)                    # the source is intact
+            for dst in range(1, n):
+                assert np.array_equal(eng.read(dst, layer), want), (layer, dst)
+                assert np.array_equal(eng.checksums(dst, layer), cs)
+                assert np.array_equal(eng.verify(dst, layer), cs)
+                assert eng.received(dst, layer) == 2 * size                    # two launches, monotonic counter
+        eng.sched_free(s)

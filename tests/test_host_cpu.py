@@ -163,3 +163,25 @@ def test_wire_format_known_answers():
     w, dec = host.msg_roundtrip(kind="layerHeader", SrcID=0, LayerID=1, LayerSize=10, TotalSize=30, Offert=20)
     assert w == '{"type":2,"src":"0","payload":{"SrcID":0,"LayerID":1,"LayerSize":10,"TotalSize":30,"Offert":20}}'
     assert dec["payload"]["Offert"] == 20             # the offset survives (the reference drops it, transport.go:221)
+
+
+def test_plan_directions_heuristic():
+    """dissem_plan_directions: pull only where the reverse NVLink ports are (nearly) idle."""
+    text = o.config_stage_ring(8, 32, o.S2)
+    xs = d.parse_plan(d.plan(text, 1, seed=0x5EED))
+    one = d.plan_directions(xs, [0] * 8)
+    assert all(x.flags == 0 for x in one)                              # one GPU: nothing crosses a link
+    two = d.plan_directions(xs, [n % 2 for n in range(8)])
+    assert all(x.flags == 0 for x in two)                              # both directions loaded: push
+    eight = d.plan_directions(xs, list(range(8)))
+    pulled = [(x.src_node, x.dst_node) for x in eight if x.flags & d.XFER_PULL]
+    assert pulled and all(s == 0 for s, _ in pulled)                   # the leader's egress dominates, its ingress is idle
+    assert all(x.flags == 0 for x in eight if x.src_node != 0)
+    # a single seed GPU: every transfer is pulled
+    seed = d.parse_plan(d.plan(o.config_stage_ring(8, 32, o.S2, ring=False), 0))
+    assert all(x.flags & d.XFER_PULL for x in d.plan_directions(seed, list(range(8))))
+    # idempotent, and the flag is cleared when the mapping changes
+    again = d.plan_directions(eight, [0] * 8)
+    assert all(x.flags == 0 for x in again)
+    with pytest.raises(d.DissemError):
+        d.plan_directions(xs, [0, 1])
