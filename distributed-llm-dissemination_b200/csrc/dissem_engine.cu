@@ -203,9 +203,14 @@ static McObject *get_or_make_mcast(dissem_ctx *ctx, int layer, int src_node, con
     return ins.first->second.valid() ? &ins.first->second : nullptr;
 }
 
+struct CompileItem {
+    dissem_xfer x;
+    McObject *mc = nullptr;      // set: one multicast stream standing for n_dsts transfers of the same bytes
+    int n_dsts = 1;
+};
+
 static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched *out) {
     if (n < 0 || (n > 0 && !xfers)) return set_error(DISSEM_EINVAL, "bad transfer list");
-    std::vector<std::vector<dissem_xfer>> by_dev(ctx->devs.size());
     for (int i = 0; i < n; ++i) {
         const dissem_xfer &x = xfers[i];
         int rc = check_node(ctx, x.src_node);
@@ -215,89 +220,101 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         if (x.size < 0 || x.off < 0 || x.off + x.size > x.total)
             return set_error(DISSEM_ERANGE, "transfer %d: [%lld,+%lld) outside layer of %lld bytes", i,
                              (long long)x.off, (long long)x.size, (long long)x.total);
-        // push (default): the GPU that holds the source runs the transfer and stores into the destination;
-        // pull: the destination's GPU runs it and loads from the (possibly remote) source.
-        const bool pull = ctx->opt_pull == 1 || (ctx->opt_pull == 0 && (x.flags & DISSEM_XFER_PULL));
-        int slot = ctx->node_dev_slot[pull ? x.dst_node : x.src_node];
+    }
+    std::vector<std::vector<CompileItem>> by_dev(ctx->devs.size());
+    std::vector<char> used((size_t)std::max(n, 1), 0);
+    auto is_pull = [&](const dissem_xfer &x) { return ctx->opt_pull == 1 || (ctx->opt_pull == 0 && (x.flags & DISSEM_XFER_PULL)); };
+
+    // Pass 1 (K2): the same bytes of one local source for several GPUs -> one NVLS multicast store stream.  This takes
+    // precedence over a transfer's PULL flag: one pushed stream that lands k times beats k pulled streams.
+    if (ctx->opt_mcast && ctx->opt_pull != 1) {
+        for (int i = 0; i < n; ++i) {
+            const dissem_xfer &x = xfers[i];
+            const int sslot = ctx->node_dev_slot[x.src_node];
+            if (used[i] || x.size == 0 || sslot < 0 || x.off % 16 || x.size % 16) continue;
+            std::vector<int> members{i};
+            for (int j = i + 1; j < n; ++j) {
+                const dissem_xfer &y = xfers[j];
+                if (!used[j] && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
+                    y.total == x.total && y.dst_node != x.dst_node)
+                    members.push_back(j);
+            }
+            const bool forced_single = ctx->opt_mcast == 2 && ctx->node_dev_slot[x.dst_node] >= 0 && ctx->node_dev_slot[x.dst_node] != sslot;
+            if (members.size() < 2 && !forced_single) continue;
+            LayerBuf *src = nullptr;
+            if (find_layer(ctx, x.src_node, x.layer, &src) || src->size != x.total) continue;   // pass 2 reports it
+            std::vector<int> dsts;
+            bool ok = true;
+            for (int m : members) {
+                LayerBuf *dl = nullptr;
+                if (find_layer(ctx, xfers[m].dst_node, x.layer, &dl) || dl->size != x.total) ok = false;
+                dsts.push_back(xfers[m].dst_node);
+            }
+            McObject *mc = ok ? get_or_make_mcast(ctx, x.layer, x.src_node, dsts) : nullptr;
+            if (!mc) continue;
+            CompileItem it;
+            it.x = x;
+            it.mc = mc;
+            it.n_dsts = (int)members.size();
+            by_dev[sslot].push_back(it);
+            for (int m : members) used[m] = 1;
+            ctx->mcast_groups_compiled++;
+        }
+    }
+    // Pass 2: everything else, executed by the source's GPU (push) or the destination's (pull)
+    for (int i = 0; i < n; ++i) {
+        if (used[i]) continue;
+        const dissem_xfer &x = xfers[i];
+        int slot = ctx->node_dev_slot[is_pull(x) ? x.dst_node : x.src_node];
         if (slot < 0) continue;          // the process that owns the executing side runs it
         if (x.size == 0) continue;       // an empty layerMsg moves nothing (LayerSize 0)
-        by_dev[slot].push_back(x);
+        CompileItem it;
+        it.x = x;
+        by_dev[slot].push_back(it);
     }
-    out->unit_shift = pick_unit_shift(ctx, by_dev);
+    {
+        std::vector<std::vector<dissem_xfer>> plain(by_dev.size());
+        for (size_t s = 0; s < by_dev.size(); ++s)
+            for (auto &it : by_dev[s]) plain[s].push_back(it.x);
+        out->unit_shift = pick_unit_shift(ctx, plain);
+    }
     for (size_t slot = 0; slot < by_dev.size(); ++slot) {
         if (by_dev[slot].empty()) continue;
         std::vector<XferDesc> descs;
         long long units = 0;
         int64_t bytes = 0;
-        std::vector<dissem_xfer> &list = by_dev[slot];
-        std::vector<char> used(list.size(), 0);
-        auto is_pull = [&](const dissem_xfer &x) { return ctx->opt_pull == 1 || (ctx->opt_pull == 0 && (x.flags & DISSEM_XFER_PULL)); };
-        for (size_t i = 0; i < list.size(); ++i) {
-            if (used[i]) continue;
-            const dissem_xfer &x = list[i];
+        for (auto &it : by_dev[slot]) {
+            const dissem_xfer &x = it.x;
             LayerBuf *src = nullptr, *dst = nullptr;
             int rc = find_layer(ctx, x.src_node, x.layer, &src);
             if (rc) return rc;
-            // the same bytes of the same source for several destinations: one multicast store stream (K2)
-            std::vector<size_t> members{i};
-            if (ctx->opt_mcast && !is_pull(x) && x.off % 16 == 0 && x.size % 16 == 0)
-                for (size_t j = i + 1; j < list.size(); ++j) {
-                    const dissem_xfer &y = list[j];
-                    if (!used[j] && !is_pull(y) && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off &&
-                        y.size == x.size && y.total == x.total && y.dst_node != x.dst_node)
-                        members.push_back(j);
-                }
-            if (members.size() >= 2 || (ctx->opt_mcast == 2 && !is_pull(x) && x.off % 16 == 0 && x.size % 16 == 0 &&
-                                        ctx->node_dev_slot[x.dst_node] != ctx->node_dev_slot[x.src_node])) {
-                std::vector<int> dsts;
-                bool sizes_ok = src->size == x.total;
-                for (size_t m : members) {
-                    dsts.push_back(list[m].dst_node);
-                    LayerBuf *dl = nullptr;
-                    if (find_layer(ctx, list[m].dst_node, x.layer, &dl) || dl->size != x.total) sizes_ok = false;
-                }
-                McObject *mc = sizes_ok ? get_or_make_mcast(ctx, x.layer, x.src_node, dsts) : nullptr;
-                if (mc) {
-                    uint8_t *mbase = reinterpret_cast<uint8_t *>(mc->va);
-                    XferDesc d;
-                    memset(&d, 0, sizeof d);
-                    d.src = src->base;
-                    d.dst = mbase;
-                    d.csum = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off() + 256);
-                    d.received = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off());
-                    d.off = x.off;
-                    d.size = x.size;
-                    d.total = x.total;
-                    d.first_unit = units;
-                    d.flags = kFlagMulticast;
-                    units += units_of(x.off, x.size, out->unit_shift);
-                    bytes += x.size * (int64_t)members.size();
-                    descs.push_back(d);
-                    for (size_t m : members) used[m] = 1;
-                    ctx->mcast_groups_compiled++;
-                    continue;
-                }
-            }
-            used[i] = 1;
-            rc = find_layer(ctx, x.dst_node, x.layer, &dst);
-            if (rc) return rc;
-            if (src->size != x.total || dst->size != x.total)
-                return set_error(DISSEM_ERANGE, "layer %d: total %lld but src holds %lld and dst %lld bytes", x.layer,
-                                 (long long)x.total, (long long)src->size, (long long)dst->size);
-            if (src->base == dst->base) return set_error(DISSEM_EINVAL, "layer %d: source and destination are the same buffer", x.layer);
             XferDesc d;
             memset(&d, 0, sizeof d);
             d.src = src->base;
-            d.dst = dst->base;
-            d.csum = dst->csum();
-            d.received = dst->received();
             d.off = x.off;
             d.size = x.size;
             d.total = x.total;
             d.first_unit = units;
-            d.flags = 0;
+            if (it.mc) {
+                uint8_t *mbase = reinterpret_cast<uint8_t *>(it.mc->va);
+                d.dst = mbase;
+                d.csum = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off() + 256);
+                d.received = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off());
+                d.flags = kFlagMulticast;
+            } else {
+                rc = find_layer(ctx, x.dst_node, x.layer, &dst);
+                if (rc) return rc;
+                if (src->size != x.total || dst->size != x.total)
+                    return set_error(DISSEM_ERANGE, "layer %d: total %lld but src holds %lld and dst %lld bytes", x.layer,
+                                     (long long)x.total, (long long)src->size, (long long)dst->size);
+                if (src->base == dst->base) return set_error(DISSEM_EINVAL, "layer %d: source and destination are the same buffer", x.layer);
+                d.dst = dst->base;
+                d.csum = dst->csum();
+                d.received = dst->received();
+                d.flags = 0;
+            }
             units += units_of(x.off, x.size, out->unit_shift);
-            bytes += x.size;
+            bytes += x.size * (int64_t)it.n_dsts;
             descs.push_back(d);
         }
         SchedPart part;
