@@ -317,6 +317,22 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             bytes += x.size * (int64_t)it.n_dsts;
             descs.push_back(d);
         }
+        // stripe order (dissem_kernels.cuh): sort by unit count, then store each level's starting ticket
+        std::stable_sort(descs.begin(), descs.end(), [&](const XferDesc &a, const XferDesc &b) {
+            return units_of(a.off, a.size, out->unit_shift) < units_of(b.off, b.size, out->unit_shift);
+        });
+        {
+            const long long m = (long long)descs.size();
+            long long sum_before = 0, prev = 0;          // sum of c_i for i < j-1 ... maintained incrementally
+            for (long long j = 0; j < m; ++j) {
+                // L_j = sum_{i<j} min(c_i, c_{j-1}) + (m-j)*c_{j-1}  ==  sum_{i<j} c_i' where all c_i <= c_{j-1}
+                descs[j].first_unit = sum_before + (m - j) * prev;
+                descs[j].prev_units = (int)prev;
+                const long long c = units_of(descs[j].off, descs[j].size, out->unit_shift);
+                sum_before += c;
+                prev = c;
+            }
+        }
         SchedPart part;
         part.dev_slot = (int)slot;
         part.n_descs = (int)descs.size();

@@ -51,16 +51,6 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
     return v;
 }
 
-// Largest d with descs[d].first_unit <= u.
-__device__ __forceinline__ int find_desc(const XferDesc *__restrict__ descs, int n, long long u) {
-    int lo = 0, hi = n - 1;
-    while (lo < hi) {
-        int mid = (lo + hi + 1) >> 1;
-        if (__ldg(&descs[mid].first_unit) <= u) lo = mid; else hi = mid - 1;
-    }
-    return lo;
-}
-
 // Per-thread checksum accumulators.  S2 uses the word offset k from the unit's first word (k < 2^17, so
 // k*w is one 32x32->64 multiply); the unit's B is (first_word_index + 1) * A + S2.
 struct Acc {
@@ -97,10 +87,11 @@ copy_csum_kernel(const XferDesc *__restrict__ descs, int n_descs, long long tota
         if (u >= total_units) break;
         if (tid == 0) s_unit[p ^ 1] = (long long)atomicAdd(&counters->ticket, 1ull);   // prefetch the next ticket
 
-        const int d = find_desc(descs, n_descs, u);
+        long long slice_idx;
+        const int d = locate_unit(descs, n_descs, u, &slice_idx);
         const XferDesc *__restrict__ D = descs + d;
         const long long off = __ldg(&D->off), size = __ldg(&D->size);
-        const long long slice = (off >> unit_shift) + (u - __ldg(&D->first_unit));
+        const long long slice = (off >> unit_shift) + slice_idx;
         long long b0 = slice << unit_shift, b1 = b0 + (1ll << unit_shift);      // byte range in LAYER space
         if (b0 < off) b0 = off;
         if (b1 > off + size) b1 = off + size;

@@ -16,7 +16,11 @@ enum : int {
 // One transfer as the kernels see it: bytes [off, off+size) of a layer, from the source copy to the
 // destination copy (distributor/transport.go:342: data[Offset : Offset+DataSize]).
 // Work units of a schedule are U-aligned slices of LAYER space (U = 1 << unit_shift <= 256 KiB), so a
-// unit never straddles a checksum chunk; first_unit is the exclusive prefix over the descriptor table.
+// unit never straddles a checksum chunk.
+// Ticket order is STRIPED over the table: round r hands out slice r of every descriptor that still has one, so at
+// any moment a source GPU is spreading its CTAs over all of its destinations (no destination is incast while another
+// idles).  The host sorts the table by unit count ascending; descriptor j then stores first_unit = L_j, the number
+// of tickets issued before round c_{j-1}, and prev_units = c_{j-1}:  L_j = sum_{i<j-1} c_i + (m-j+1)*c_{j-1}.
 struct __align__(16) XferDesc {
     const uint8_t *src;              // source layer base (local HBM)
     uint8_t *dst;                    // destination layer base: local, peer-mapped or multicast; NULL = checksum only
@@ -25,9 +29,10 @@ struct __align__(16) XferDesc {
     long long off;                   // fragment start within the layer
     long long size;                  // fragment bytes (> 0)
     long long total;                 // full layer size
-    long long first_unit;            // exclusive prefix of unit counts
+    long long first_unit;            // stripe level start: tickets issued before round prev_units (see locate_unit)
     int flags;
-    int pad[3];
+    int prev_units;                  // unit count of the previous (shorter) descriptor in the table, 0 for the first
+    int pad[2];
 };
 static_assert(sizeof(XferDesc) == 80, "XferDesc layout");
 
@@ -60,6 +65,22 @@ cudaError_t launch_copy_csum(const XferDesc *descs, int n_descs, long long total
 // Synthetic contents (DISSEM_FILL_PATTERN).
 cudaError_t launch_fill_pattern(uint8_t *dst, long long size, unsigned long long layer_id,
                                 unsigned long long seed, int n_sm, cudaStream_t stream);
+
+#ifdef __CUDACC__
+// ticket -> (descriptor, slice index within it).  Largest j with L_j <= t; within level j the (m - j) longest
+// descriptors take turns.
+__device__ __forceinline__ int locate_unit(const XferDesc *__restrict__ descs, int n, long long t, long long *slice_idx) {
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(&descs[mid].first_unit) <= t) lo = mid; else hi = mid - 1;
+    }
+    const long long q = t - __ldg(&descs[lo].first_unit);
+    const int active = n - lo;
+    *slice_idx = (long long)__ldg(&descs[lo].prev_units) + q / active;
+    return lo + (int)(q % active);
+}
+#endif
 
 // Number of units a fragment occupies for a given unit size.
 static inline long long units_of(long long off, long long size, int unit_shift) {

@@ -103,15 +103,6 @@ __device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
     return v;
 }
 
-__device__ __forceinline__ int find_desc_tma(const XferDesc *__restrict__ descs, int n, long long u) {
-    int lo = 0, hi = n - 1;
-    while (lo < hi) {
-        int mid = (lo + hi + 1) >> 1;
-        if (__ldg(&descs[mid].first_unit) <= u) lo = mid; else hi = mid - 1;
-    }
-    return lo;
-}
-
 template <int kStageBytes, int kStages, int kStoreLag>
 __global__ void __launch_bounds__(kThreadsTma, 1)
 copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long total_units, int unit_shift,
@@ -142,9 +133,10 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
                 const XferDesc *D = nullptr;
                 long long b0 = 0, b1 = 0, a0 = 0, a1 = 0;
                 if (!end) {
-                    D = descs + find_desc_tma(descs, n_descs, u);
+                    long long slice_idx;
+                    D = descs + locate_unit(descs, n_descs, u, &slice_idx);
                     const long long off = D->off, size = D->size;
-                    const long long slice = (off >> unit_shift) + (u - D->first_unit);
+                    const long long slice = (off >> unit_shift) + slice_idx;
                     b0 = slice << unit_shift;
                     b1 = b0 + (1ll << unit_shift);
                     if (b0 < off) b0 = off;

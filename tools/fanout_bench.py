@@ -49,9 +49,10 @@ def t_star(xfers, n, multicast):
     return max(max(e, i) for e, i in zip(eg, ing)) / (LINK_GBPS * 1e9), eg, ing
 
 
-def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps):
+def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, variant=1):
     eng = d.Engine(list(range(n)))
     try:
+        eng.set_option("variant", variant)
         eng.set_option("alloc_vmm", 1 if vmm else 0)
         eng.set_option("mcast", mcast)
         for l, seed in holders.items():
@@ -105,6 +106,9 @@ def main():
         run_case(f"{tag}/unicast auto direction", n, holders, xfers, args.size, vmm=False, mcast=0, directions=True, reps=args.reps)
     if "mcast" in cases:
         run_case(f"{tag}/NVLS multicast", n, holders, xfers, args.size, vmm=True, mcast=1, directions=False, reps=args.reps)
+    if "mcast_reg" in cases:
+        run_case(f"{tag}/NVLS multicast (register kernel)", n, holders, xfers, args.size, vmm=True, mcast=1, directions=False,
+                 reps=args.reps, variant=0)
     if "mcast_auto" in cases:
         run_case(f"{tag}/NVLS multicast + auto direction for the rest", n, holders, xfers, args.size, vmm=True, mcast=1,
                  directions=True, reps=args.reps)
