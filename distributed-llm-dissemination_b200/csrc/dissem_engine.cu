@@ -228,38 +228,72 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
     // Pass 1 (K2): the same bytes of one local source for several GPUs -> one NVLS multicast store stream.  This takes
     // precedence over a transfer's PULL flag: one pushed stream that lands k times beats k pulled streams.
     if (ctx->opt_mcast && ctx->opt_pull != 1) {
+        struct Group { std::vector<int> members; };
+        std::vector<Group> groups;
+        std::vector<char> grouped((size_t)std::max(n, 1), 0);
         for (int i = 0; i < n; ++i) {
             const dissem_xfer &x = xfers[i];
             const int sslot = ctx->node_dev_slot[x.src_node];
-            if (used[i] || x.size == 0 || sslot < 0 || x.off % 16 || x.size % 16) continue;
-            std::vector<int> members{i};
+            if (grouped[i] || x.size == 0 || sslot < 0 || x.off % 16 || x.size % 16) continue;
+            Group g;
+            g.members.push_back(i);
             for (int j = i + 1; j < n; ++j) {
                 const dissem_xfer &y = xfers[j];
-                if (!used[j] && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
+                if (!grouped[j] && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
                     y.total == x.total && y.dst_node != x.dst_node)
-                    members.push_back(j);
+                    g.members.push_back(j);
             }
             const bool forced_single = ctx->opt_mcast == 2 && ctx->node_dev_slot[x.dst_node] >= 0 && ctx->node_dev_slot[x.dst_node] != sslot;
-            if (members.size() < 2 && !forced_single) continue;
-            LayerBuf *src = nullptr;
-            if (find_layer(ctx, x.src_node, x.layer, &src) || src->size != x.total) continue;   // pass 2 reports it
-            std::vector<int> dsts;
-            bool ok = true;
-            for (int m : members) {
-                LayerBuf *dl = nullptr;
-                if (find_layer(ctx, xfers[m].dst_node, x.layer, &dl) || dl->size != x.total) ok = false;
-                dsts.push_back(xfers[m].dst_node);
-            }
-            McObject *mc = ok ? get_or_make_mcast(ctx, x.layer, x.src_node, dsts) : nullptr;
-            if (!mc) continue;
-            CompileItem it;
-            it.x = x;
-            it.mc = mc;
-            it.n_dsts = (int)members.size();
-            by_dev[sslot].push_back(it);
-            for (int m : members) used[m] = 1;
-            ctx->mcast_groups_compiled++;
+            if (g.members.size() < 2 && !forced_single) continue;
+            for (int m : g.members) grouped[m] = 1;
+            groups.push_back(std::move(g));
         }
+        // Cost model (opt_mcast == 1).  Measured on B200 / NVLink 5 (profiles/r01_summary.md): a unicast push stream
+        // moves ~710 GB/s per port; an NVLS multicast stream leaves its source at ~634 GB/s but lands at only
+        // ~537 GB/s per destination port.  Multicast therefore pays only when the plan is bound by a source's egress:
+        // compare max-port time with every group sent as unicast copies against every group sent once.
+        bool use_mc = !groups.empty();
+        if (ctx->opt_mcast == 1 && use_mc) {
+            auto gpu_of = [&](int node) { int sl = ctx->node_dev_slot[node]; return sl >= 0 ? ctx->devs[sl].dev : 1000 + node; };
+            std::map<int, double> eg_uni, eg_mc, ing;
+            for (int i = 0; i < n; ++i) {
+                const dissem_xfer &x = xfers[i];
+                const int gs = gpu_of(x.src_node), gd = gpu_of(x.dst_node);
+                if (gs == gd) continue;
+                eg_uni[gs] += (double)x.size;
+                ing[gd] += (double)x.size;
+                if (!grouped[i]) eg_mc[gs] += (double)x.size;
+            }
+            for (auto &g : groups) eg_mc[gpu_of(xfers[g.members[0]].src_node)] += (double)xfers[g.members[0]].size;
+            auto mx = [](const std::map<int, double> &m) { double v = 0; for (auto &kv : m) v = std::max(v, kv.second); return v; };
+            const double t_uni = std::max(mx(eg_uni), mx(ing)) / 710.0;
+            const double t_mc = std::max(mx(eg_mc) / 634.0, mx(ing) / 537.0);
+            use_mc = t_mc < t_uni;
+            if (!use_mc) ctx->mcast_note = "cost model: the plan is not egress-bound, unicast copies are faster than multicast";
+        }
+        if (use_mc)
+            for (auto &g : groups) {
+                const dissem_xfer &x = xfers[g.members[0]];
+                const int sslot = ctx->node_dev_slot[x.src_node];
+                LayerBuf *src = nullptr;
+                if (find_layer(ctx, x.src_node, x.layer, &src) || src->size != x.total) continue;   // pass 2 reports it
+                std::vector<int> dsts;
+                bool ok = true;
+                for (int m : g.members) {
+                    LayerBuf *dl = nullptr;
+                    if (find_layer(ctx, xfers[m].dst_node, x.layer, &dl) || dl->size != x.total) ok = false;
+                    dsts.push_back(xfers[m].dst_node);
+                }
+                McObject *mc = ok ? get_or_make_mcast(ctx, x.layer, x.src_node, dsts) : nullptr;
+                if (!mc) continue;
+                CompileItem it;
+                it.x = x;
+                it.mc = mc;
+                it.n_dsts = (int)g.members.size();
+                by_dev[sslot].push_back(it);
+                for (int m : g.members) used[m] = 1;
+                ctx->mcast_groups_compiled++;
+            }
     }
     // Pass 2: everything else, executed by the source's GPU (push) or the destination's (pull)
     for (int i = 0; i < n; ++i) {
@@ -942,7 +976,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
     else if (k == "tma_cfg") { if (value < 0 || value > 5) return set_error(DISSEM_EINVAL, "tma_cfg must be 0..5"); ctx->opt_tma_cfg = value; }
     else if (k == "alloc_vmm") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0 or 1"); ctx->opt_alloc_vmm = value; }
-    else if (k == "mcast") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "mcast must be 0, 1 or 2"); ctx->opt_mcast = value; }
+    else if (k == "mcast") { if (value < 0 || value > 3) return set_error(DISSEM_EINVAL, "mcast must be 0..3"); ctx->opt_mcast = value; }
     else if (k == "pull") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "pull must be 0, 1 or 2"); ctx->opt_pull = value; }
     else if (k == "reg_cfg") { if (value < 0 || value > 6) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..6"); ctx->opt_reg_cfg = value; }
     else if (k == "unit_bytes") {

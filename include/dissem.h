@@ -183,9 +183,10 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
  * "tma_cfg" (TMA ring shape, stage bytes x stages: 0 16Kx6 (default), 1 32Kx3, 2 8Kx12, 3 16Kx4, 4 8Kx6, 5 4Kx12),
  * "alloc_vmm" (1 = dissem_layer_alloc uses the VMM API so that layers can be bound to NVLS multicast objects;
  *  such layers cannot be exported to other processes yet),
- * "mcast" (1 (default) = transfers of the same bytes from one source to several GPUs are sent as ONE NVLS
- *  multicast store stream when every buffer involved is VMM-backed and local; 0 = always unicast fan-out;
- *  2 = also route single-destination transfers to another GPU through a multicast object (a testing aid)),
+ * "mcast" (transfers of the same bytes from one source to several GPUs can go as ONE NVLS multicast store stream
+ *  when every buffer involved is VMM-backed and local.  1 (default) = do so when a cost model built on the measured
+ *  port rates says the plan gets shorter (i.e. it is bound by a source's egress); 3 = always; 0 = never (unicast
+ *  fan-out); 2 = always, and single-destination transfers to another GPU too (a testing aid)),
  * read-only: "mcast_supported" (do all local GPUs support multicast objects), "mcast_groups" (multicast
  *  descriptors compiled so far),
  * "unit_bytes" (0 = auto; else power of two in [4096, 262144]),

@@ -91,7 +91,7 @@ def main():
     ap.add_argument("--size", type=int, default=1_711_308_800)
     ap.add_argument("--one-seed", action="store_true")
     ap.add_argument("--reps", type=int, default=5)
-    ap.add_argument("--cases", default="unicast,auto,mcast")
+    ap.add_argument("--cases", default="unicast,auto,mcast,default")
     args = ap.parse_args()
     n = min(torch.cuda.device_count(), 8)
     if n < 3:
@@ -105,9 +105,12 @@ def main():
     if "auto" in cases:
         run_case(f"{tag}/unicast auto direction", n, holders, xfers, args.size, vmm=False, mcast=0, directions=True, reps=args.reps)
     if "mcast" in cases:
-        run_case(f"{tag}/NVLS multicast", n, holders, xfers, args.size, vmm=True, mcast=1, directions=False, reps=args.reps)
+        run_case(f"{tag}/NVLS multicast (always)", n, holders, xfers, args.size, vmm=True, mcast=3, directions=False, reps=args.reps)
+    if "default" in cases:
+        run_case(f"{tag}/default: cost-model multicast + auto direction", n, holders, xfers, args.size, vmm=True, mcast=1,
+                 directions=True, reps=args.reps)
     if "mcast_reg" in cases:
-        run_case(f"{tag}/NVLS multicast (register kernel)", n, holders, xfers, args.size, vmm=True, mcast=1, directions=False,
+        run_case(f"{tag}/NVLS multicast (register kernel)", n, holders, xfers, args.size, vmm=True, mcast=3, directions=False,
                  reps=args.reps, variant=0)
     if "mcast_auto" in cases:
         run_case(f"{tag}/NVLS multicast + auto direction for the rest", n, holders, xfers, args.size, vmm=True, mcast=1,
