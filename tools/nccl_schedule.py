@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--size", type=int, default=1_711_308_800)
     ap.add_argument("--one-seed", action="store_true")
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--bcast", action="store_true", help="also run the broadcast-per-layer rendition (did not finish on the 8-GPU box)")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -82,6 +83,10 @@ def main():
         print(json.dumps({"case": f"{tag}/NCCL grouped send-recv", "n_gpus": world, "completion_ms_best": t_sr * 1e3,
                           "aggregate_GBps": D / t_sr / 1e9, "delivered_bytes": D, "verified": ok}), flush=True)
 
+    if not args.bcast:
+        dist.barrier()
+        dist.destroy_process_group()
+        return
     # (b) broadcast per layer on a sub-communicator
     groups = {}
     for l, seed, dsts in plan:
