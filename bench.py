@@ -362,15 +362,16 @@ def run_ours(args, rank, world, local_rank):
         # algorithmic bytes of the dominant kernel: local copy = 2*S HBM bytes per delivered byte
         alg_bytes = 2 * my_bytes if local else my_bytes
         achieved = alg_bytes / (copy_ms_avg / 1e3) / 1e9 if copy_ms_avg > 0 else 0.0
+        kernel_name = "copy_csum_tma_kernel" if args.variant == 1 else "copy_csum_kernel"
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
             try:
-                traffic = json.load(open(tpath)).get("copy_csum_dram_bytes_per_launch")
+                traffic = json.load(open(tpath)).get(kernel_name + "_dram_bytes_per_launch")
             except Exception:
                 traffic = None
         roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "copy_csum_kernel", "peak_source": peak_src,
+                "traffic": traffic, "kernel": kernel_name, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": copy_ms_avg}
         if not local:
             # NVLink roofline of the placement: T* = max over GPUs of max(egress, ingress) / link bandwidth, plus that
@@ -380,7 +381,7 @@ def run_ours(args, rank, world, local_rank):
             t_star = max(max(e, i) / (link * 1e9) + 2 * l / (peak * 1e9) for e, i, l in zip(eg, ing, loc))
             busiest = max(max(e, i) for e, i in zip(eg, ing))
             roof = {"bound": "nvlink", "achieved": busiest / dev_step_s / 1e9, "peak": link, "unit": "GB/s",
-                    "frac": t_star / dev_step_s, "traffic": None, "kernel": "copy_csum_kernel",
+                    "frac": t_star / dev_step_s, "traffic": None, "kernel": kernel_name,
                     "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
                     "algorithmic_bytes_per_launch": busiest, "launch_ms": dev_step_s * 1e3,
                     "egress_bytes": eg, "ingress_bytes": ing, "local_bytes": loc, "t_star_ms": t_star * 1e3,
