@@ -96,7 +96,7 @@ class ClockSampler:
                           ("sw_power_cap", 0x4)):
             if r & bit:
                 names.append(name)
-        self.rows.append((sm, mx, names))
+        self.rows.append((time.perf_counter(), sm, mx, names))
 
     def _sample_smi(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -107,7 +107,7 @@ class ClockSampler:
             c = [v.strip() for v in out.split(",")]
             names = [n for n, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[2:6])
                      if v.lower().startswith("active")]
-            self.rows.append((int(float(c[0])), int(float(c[1])), names))
+            self.rows.append((time.perf_counter(), int(float(c[0])), int(float(c[1])), names))
 
     def _run(self):
         while not self._stop.is_set():
@@ -129,10 +129,17 @@ class ClockSampler:
         self._stop.set()
         self._t.join(timeout=6)
 
-    def summary(self):
-        sm = sorted(r[0] for r in self.rows)
-        reasons = sorted({n for r in self.rows for n in r[2]})
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[1] for r in self.rows), default=None),
+    def wait_first(self, timeout=3.0):
+        end = time.perf_counter() + timeout
+        while not self.rows and time.perf_counter() < end:
+            time.sleep(0.005)
+
+    def summary(self, t0=None, t1=None):
+        """Samples taken between t0 and t1 (perf_counter), i.e. inside the timed region."""
+        rows = [r for r in self.rows if (t0 is None or r[0] >= t0) and (t1 is None or r[0] <= t1)]
+        sm = sorted(r[1] for r in rows)
+        reasons = sorted({n for r in rows for n in r[3]})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[2] for r in rows), default=None),
                 "reasons": reasons, "samples": len(sm), "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
@@ -251,15 +258,17 @@ def run_ours(args, rank, world, local_rank):
     assert sched_bytes == my_bytes
 
     # ---- device-resident throughput -------------------------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
-        eng.wait(eng.launch(sched))
-    barrier()
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank) as clocks:          # started before the warm-up so that NVML is warm; filtered below
+        for _ in range(max(args.warmup, 3)):
+            eng.wait(eng.launch(sched))
+        clocks.wait_first()
+        barrier()
         t0 = time.perf_counter()
         tickets = [eng.launch(sched) for _ in range(args.steps)]
         times = [eng.wait_detail(t) for t in tickets]
         barrier()
-        wall = time.perf_counter() - t0
+        t1 = time.perf_counter()
+        wall = t1 - t0
     dev_ms_total = sum(t[0] for t in times)
     copy_ms_avg = sum(t[1] for t in times) / max(len(times), 1)
     t_all = torch.tensor([wall, dev_ms_total], dtype=torch.float64, device="cuda")
@@ -401,7 +410,7 @@ def run_ours(args, rank, world, local_rank):
                     "what": "pinned host layers -> dissem_layer_write -> dissem_plan_json -> dissem_schedule_submit -> "
                             "dissem_wait -> dissem_layer_checksums"},
             "gpu_launches": launches_per_step * args.steps,
-            "clocks": clocks.summary(),
+            "clocks": clocks.summary(t0, t1),
             "roofline": roof,
             "cpu_baseline": cpu,
             "verified": ok,
