@@ -460,6 +460,7 @@ int dissem_init(int n_nodes, const int *device_of_node, dissem_ctx **out) {
             CUDA_TRY(cudaStreamCreateWithFlags(&ds.stream, cudaStreamNonBlocking));
             CUDA_TRY(cudaMalloc(&ds.counters, sizeof(SchedCounters)));
             CUDA_TRY(cudaMemset(ds.counters, 0, sizeof(SchedCounters)));
+            CUDA_TRY(warm_kernels());
             ctx->devs.push_back(ds);
             slot = (int)ctx->devs.size() - 1;
         }

@@ -290,6 +290,17 @@ cudaError_t launch_copy_csum(const XferDesc *descs, int n_descs, long long total
     }
 }
 
+cudaError_t warm_kernels_tma();   // dissem_kernels_tma.cu
+
+cudaError_t warm_kernels() {
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, copy_csum_kernel<512, 4>);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, zero_csum_kernel);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, fill_pattern_kernel);
+    if (e == cudaSuccess) e = warm_kernels_tma();
+    return e;
+}
+
 cudaError_t launch_fill_pattern(uint8_t *dst, long long size, unsigned long long layer_id,
                                 unsigned long long seed, int n_sm, cudaStream_t stream) {
     if (size <= 0) return cudaSuccess;

@@ -62,6 +62,10 @@ cudaError_t launch_copy_csum(const XferDesc *descs, int n_descs, long long total
                              SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream,
                              int *grid_out);
 
+// Force the module with these kernels to load on the current device (CUDA loads lazily: without this the first
+// transfer of a run would pay the load inside its timed region).
+cudaError_t warm_kernels();
+
 // Synthetic contents (DISSEM_FILL_PATTERN).
 cudaError_t launch_fill_pattern(uint8_t *dst, long long size, unsigned long long layer_id,
                                 unsigned long long seed, int n_sm, cudaStream_t stream);

@@ -330,6 +330,11 @@ static cudaError_t launch_tma(const XferDesc *descs, int n_descs, long long tota
 
 }  // namespace
 
+cudaError_t warm_kernels_tma() {
+    cudaFuncAttributes a;
+    return cudaFuncGetAttributes(&a, copy_csum_tma_kernel<16384, 6, 3>);
+}
+
 cudaError_t launch_copy_csum_tma(const XferDesc *descs, int n_descs, long long total_units, int unit_shift,
                                  SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream, int *grid_out) {
     switch (cfg.tma_cfg) {

@@ -433,3 +433,15 @@ def test_multicast_fanout_matches_unicast():
                 assert np.array_equal(eng.verify(dst, layer), cs)
                 assert eng.received(dst, layer) == 2 * size                    # two launches, monotonic counter
         eng.sched_free(s)
+
+
+@pytest.mark.parametrize("mode,batched", [(0, False), (1, True), (3, True), (3, False)])
+def test_roles_across_gpus(mode, batched):
+    """Leader + receivers with each node on its own GPU (one process): layerMsg bodies cross NVLink."""
+    n = min(_n_gpus(), 4)
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    text = o.config_stage_ring(4, 8, 3 * d.CHUNK_BYTES + 1001, ring=(mode == 1))
+    r = host.run_distribution(text, mode, node_device=[i % n for i in range(4)], batched=batched, seed=SEED,
+                              time_scale=1_000_000, timeout_ms=20000)
+    assert r["verified"] and r["ready_equals_assignment"] and r["layers_checked"] == 6

@@ -71,3 +71,26 @@ def test_link_bytes_roofline_inputs():
     assert max(ing) == 4 * o.S2                                                      # each receiver takes its stage
     eg1, ing1, loc1 = multi.link_bytes(xf, multi.owner_round_robin(1), 1)
     assert eg1 == [0] and loc1 == [28 * o.S2]
+
+
+def test_pull_flags_swap_exports_and_imports():
+    text = o.config_stage_ring(8, 32, o.S2)
+    xf = d.plan_directions(d.parse_plan(d.plan(text, 1, seed=0x5EED)), list(range(8)))
+    owner = multi.owner_round_robin(8)
+    pulled = [x for x in xf if x.flags & d.XFER_PULL]
+    assert pulled
+    for rank in range(8):
+        mine = multi.my_transfers(xf, owner, rank)
+        for x in mine:
+            assert owner(x.dst_node if x.flags & 1 else x.src_node) == rank
+        for (n, l, _t) in multi.imports_needed(xf, owner, rank):
+            assert owner(n) != rank
+        for (n, l, _t) in multi.exports_needed(xf, owner, rank):
+            assert owner(n) == rank
+    # every import is somebody's export
+    imp = {t for r in range(8) for t in multi.imports_needed(xf, owner, r)}
+    exp = {t for r in range(8) for t in multi.exports_needed(xf, owner, r)}
+    assert imp == exp
+    # the leader exports the SOURCE layers that are pulled from it, and imports nothing for them
+    assert {(n, l) for (n, l, _t) in multi.exports_needed(xf, owner, 0)} == {(0, x.layer) for x in pulled}
+    assert sum(len(multi.my_transfers(xf, owner, r)) for r in range(8)) == len(xf)
