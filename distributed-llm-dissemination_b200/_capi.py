@@ -73,6 +73,7 @@ def load_library() -> ctypes.CDLL:
         "dissem_schedule_free": (c.c_int, [P, i64]),
         "dissem_schedule_info": (c.c_int, [P, i64, c.POINTER(i64), c.POINTER(c.c_int), c.POINTER(i64)]),
         "dissem_plan_directions": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int]),
+        "dissem_plan_relay": (c.c_int, [c.POINTER(Xfer), c.c_int, c.c_int, c.POINTER(c.POINTER(Xfer)), c.POINTER(c.c_int)]),
         "dissem_wait": (c.c_int, [P, i64, c.POINTER(c.c_double)]),
         "dissem_wait_detail": (c.c_int, [P, i64, c.POINTER(c.c_double), c.POINTER(c.c_double)]),
         "dissem_poll": (c.c_int, [P, i64, c.POINTER(c.c_int)]),
@@ -125,6 +126,25 @@ def plan_directions(xfers: List["Xfer"], gpu_of_node: Sequence[int]) -> List["Xf
     g = (ctypes.c_int * len(gpu_of_node))(*gpu_of_node)
     _check(lib().dissem_plan_directions(arr, len(xfers), g, len(gpu_of_node)))
     return [Xfer(a.src_node, a.dst_node, a.layer, a.flags, a.off, a.size, a.total) for a in arr[:len(xfers)]]
+
+
+def xfer_round(x: "Xfer") -> int:
+    return (x.flags >> 8) & 0xFFFF
+
+
+def plan_relay(xfers: List["Xfer"], pieces: int = 16) -> List["Xfer"]:
+    """dissem_plan_relay: multi-destination transfers become piece-pipelined chains over rounds."""
+    arr = make_xfers(xfers)
+    out = ctypes.POINTER(Xfer)()
+    n_out = ctypes.c_int()
+    L = lib()
+    _check(L.dissem_plan_relay(arr, len(xfers), pieces, ctypes.byref(out), ctypes.byref(n_out)))
+    res = [Xfer(out[i].src_node, out[i].dst_node, out[i].layer, out[i].flags, out[i].off, out[i].size, out[i].total)
+           for i in range(n_out.value)]
+    L.dissem_free.restype = None
+    L.dissem_free.argtypes = [ctypes.c_void_p]
+    L.dissem_free(ctypes.cast(out, ctypes.c_void_p))
+    return res
 
 
 NOALLOC_MAX_CHUNKS = 8192

@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -66,6 +67,7 @@ struct DeviceState {
 
 struct SchedPart {
     int dev_slot = -1;
+    int round = 0;
     XferDesc *d_descs = nullptr;
     int n_descs = 0;
     long long total_units = 0;
@@ -221,10 +223,18 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             return set_error(DISSEM_ERANGE, "transfer %d: [%lld,+%lld) outside layer of %lld bytes", i,
                              (long long)x.off, (long long)x.size, (long long)x.total);
     }
-    std::vector<std::vector<CompileItem>> by_dev(ctx->devs.size());
+    // Rounds (DISSEM_XFER_ROUND): transfers of round r start after every transfer of round r-1 has completed on every
+    // GPU of this process; a relay plan forwards in round r what arrived in round r-1.
+    auto round_of = [](const dissem_xfer &x) { return (int)((x.flags >> DISSEM_XFER_ROUND_SHIFT) & 0xFFFF); };
+    std::vector<int> rounds;
+    for (int i = 0; i < n; ++i) rounds.push_back(round_of(xfers[i]));
+    std::sort(rounds.begin(), rounds.end());
+    rounds.erase(std::unique(rounds.begin(), rounds.end()), rounds.end());
+    std::vector<std::vector<std::vector<CompileItem>>> assigned;          // [round index][device slot]
     std::vector<char> used((size_t)std::max(n, 1), 0);
     auto is_pull = [&](const dissem_xfer &x) { return ctx->opt_pull == 1 || (ctx->opt_pull == 0 && (x.flags & DISSEM_XFER_PULL)); };
-
+    for (int cur_round : rounds) {
+    std::vector<std::vector<CompileItem>> by_dev(ctx->devs.size());
     // Pass 1 (K2): the same bytes of one local source for several GPUs -> one NVLS multicast store stream.  This takes
     // precedence over a transfer's PULL flag: one pushed stream that lands k times beats k pulled streams.
     if (ctx->opt_mcast && ctx->opt_pull != 1) {
@@ -234,13 +244,13 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         for (int i = 0; i < n; ++i) {
             const dissem_xfer &x = xfers[i];
             const int sslot = ctx->node_dev_slot[x.src_node];
-            if (grouped[i] || x.size == 0 || sslot < 0 || x.off % 16 || x.size % 16) continue;
+            if (grouped[i] || round_of(x) != cur_round || x.size == 0 || sslot < 0 || x.off % 16 || x.size % 16) continue;
             Group g;
             g.members.push_back(i);
             for (int j = i + 1; j < n; ++j) {
                 const dissem_xfer &y = xfers[j];
-                if (!grouped[j] && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
-                    y.total == x.total && y.dst_node != x.dst_node)
+                if (!grouped[j] && round_of(y) == cur_round && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off &&
+                    y.size == x.size && y.total == x.total && y.dst_node != x.dst_node)
                     g.members.push_back(j);
             }
             const bool forced_single = ctx->opt_mcast == 2 && ctx->node_dev_slot[x.dst_node] >= 0 && ctx->node_dev_slot[x.dst_node] != sslot;
@@ -259,7 +269,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             for (int i = 0; i < n; ++i) {
                 const dissem_xfer &x = xfers[i];
                 const int gs = gpu_of(x.src_node), gd = gpu_of(x.dst_node);
-                if (gs == gd) continue;
+                if (gs == gd || round_of(x) != cur_round) continue;
                 eg_uni[gs] += (double)x.size;
                 ing[gd] += (double)x.size;
                 if (!grouped[i]) eg_mc[gs] += (double)x.size;
@@ -297,7 +307,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
     }
     // Pass 2: everything else, executed by the source's GPU (push) or the destination's (pull)
     for (int i = 0; i < n; ++i) {
-        if (used[i]) continue;
+        if (used[i] || round_of(xfers[i]) != cur_round) continue;
         const dissem_xfer &x = xfers[i];
         int slot = ctx->node_dev_slot[is_pull(x) ? x.dst_node : x.src_node];
         if (slot < 0) continue;          // the process that owns the executing side runs it
@@ -306,12 +316,17 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         it.x = x;
         by_dev[slot].push_back(it);
     }
-    {
+    assigned.push_back(std::move(by_dev));
+    }   // per round
+    out->unit_shift = kChunkShift;
+    for (auto &by_dev : assigned) {
         std::vector<std::vector<dissem_xfer>> plain(by_dev.size());
         for (size_t s = 0; s < by_dev.size(); ++s)
             for (auto &it : by_dev[s]) plain[s].push_back(it.x);
-        out->unit_shift = pick_unit_shift(ctx, plain);
+        out->unit_shift = std::min(out->unit_shift, pick_unit_shift(ctx, plain));
     }
+    for (size_t ri = 0; ri < assigned.size(); ++ri) {
+    auto &by_dev = assigned[ri];
     for (size_t slot = 0; slot < by_dev.size(); ++slot) {
         if (by_dev[slot].empty()) continue;
         std::vector<XferDesc> descs;
@@ -369,6 +384,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         }
         SchedPart part;
         part.dev_slot = (int)slot;
+        part.round = rounds[ri];
         part.n_descs = (int)descs.size();
         part.total_units = units;
         part.bytes = bytes;
@@ -381,13 +397,24 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         out->units += units;
         out->bytes += bytes;
     }
+    }   // per round
     return 0;
 }
 
 static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
+    // parts are ordered by round; a round's kernels wait (on the device, cudaStreamWaitEvent) for the end events of
+    // the previous round on every GPU of this process
+    std::vector<cudaEvent_t> prev_round, cur_round;
+    int round = s.parts.empty() ? 0 : s.parts[0].round;
     for (auto &p : s.parts) {
+        if (p.round != round) {
+            prev_round.swap(cur_round);
+            cur_round.clear();
+            round = p.round;
+        }
         DeviceState &ds = ctx->devs[p.dev_slot];
         CUDA_TRY(cudaSetDevice(ds.dev));
+        for (cudaEvent_t ev : prev_round) CUDA_TRY(cudaStreamWaitEvent(ds.stream, ev, 0));
         TicketPart tp;
         tp.dev_slot = p.dev_slot;
         CUDA_TRY(cudaEventCreate(&tp.start));
@@ -400,6 +427,7 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
         LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
         CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
         CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
+        cur_round.push_back(tp.end);
     }
     return 0;
 }
@@ -827,6 +855,62 @@ int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, in
     return DISSEM_OK;
 }
 
+int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **out, int *n_out) {
+    if (n < 0 || (n > 0 && !in) || !out || !n_out || pieces < 1 || pieces > 4096)
+        return set_error(DISSEM_EINVAL, "dissem_plan_relay: bad arguments");
+    std::vector<dissem_xfer> res;
+    std::vector<char> used((size_t)std::max(n, 1), 0);
+    auto emit = [&](int src, int dst, const dissem_xfer &x, int hop) {
+        // pieces are cut at multiples of the checksum chunk in LAYER space, so every piece owns whole chunks
+        int64_t piece = (x.size + pieces - 1) / pieces;
+        piece = (piece + DISSEM_CHUNK_BYTES - 1) / DISSEM_CHUNK_BYTES * DISSEM_CHUNK_BYTES;
+        if (piece <= 0) piece = DISSEM_CHUNK_BYTES;
+        int64_t pos = x.off;
+        const int64_t end = x.off + x.size;
+        for (int p = 0; pos < end; ++p) {
+            int64_t stop = (pos / piece + 1) * piece;            // next piece boundary in layer space
+            if (stop > end) stop = end;
+            dissem_xfer y = x;
+            y.src_node = src;
+            y.dst_node = dst;
+            y.off = pos;
+            y.size = stop - pos;
+            y.flags = (x.flags & ~(0xFFFF << DISSEM_XFER_ROUND_SHIFT) & ~DISSEM_XFER_PULL) | DISSEM_XFER_ROUND(p + hop);
+            res.push_back(y);
+            pos = stop;
+        }
+    };
+    for (int i = 0; i < n; ++i) {
+        if (used[i]) continue;
+        const dissem_xfer &x = in[i];
+        used[i] = 1;
+        if (x.size <= 0) { res.push_back(x); continue; }
+        std::vector<int> dsts{x.dst_node};
+        for (int j = i + 1; j < n; ++j) {
+            const dissem_xfer &y = in[j];
+            if (!used[j] && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
+                y.total == x.total && y.dst_node != x.dst_node) {
+                dsts.push_back(y.dst_node);
+                used[j] = 1;
+            }
+        }
+        std::sort(dsts.begin(), dsts.end());
+        // rotate so that the first hop (which forwards the most) is not always the same node
+        std::rotate(dsts.begin(), dsts.begin() + (size_t)((unsigned)x.layer % dsts.size()), dsts.end());
+        int prev = x.src_node;
+        for (size_t h = 0; h < dsts.size(); ++h) {
+            emit(prev, dsts[h], x, (int)h);                      // hop h forwards in round p+h what arrived in round p+h-1
+            prev = dsts[h];
+        }
+    }
+    dissem_xfer *buf = (dissem_xfer *)malloc(std::max<size_t>(res.size(), 1) * sizeof(dissem_xfer));
+    if (!buf) return set_error(DISSEM_ENOMEM, "out of memory");
+    memcpy(buf, res.data(), res.size() * sizeof(dissem_xfer));
+    *out = buf;
+    *n_out = (int)res.size();
+    return DISSEM_OK;
+}
+
 int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out) { return dissem_wait_detail(ctx, ticket, ms_out, nullptr); }
 
 int dissem_wait_detail(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out, double *copy_ms_out) {
@@ -842,21 +926,31 @@ int dissem_wait_detail(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out, do
     // wait outside the lock: other goroutines keep calling Send meanwhile (node.go:343)
     double ms = 0.0, copy_ms = 0.0;
     int rc = DISSEM_OK;
+    std::map<int, std::pair<cudaEvent_t, cudaEvent_t>> span;      // device slot -> (first start, last end)
+    std::map<int, double> copy_sum;
     for (auto &p : t.parts) {
         cudaError_t e = cudaEventSynchronize(p.end);
         if (e != cudaSuccess) {
             rc = set_error(DISSEM_ECUDA, "transfer failed: %s", cudaGetErrorString(e));
             break;
         }
+        auto it = span.find(p.dev_slot);
+        if (it == span.end()) span[p.dev_slot] = std::make_pair(p.start, p.end);
+        else it->second.second = p.end;
         float f = 0.f;
-        e = cudaEventElapsedTime(&f, p.start, p.end);
-        if (e != cudaSuccess) {
-            rc = set_error(DISSEM_ECUDA, "cudaEventElapsedTime: %s", cudaGetErrorString(e));
-            break;
-        }
-        ms = std::max(ms, (double)f);
-        if (cudaEventElapsedTime(&f, p.mid, p.end) == cudaSuccess) copy_ms = std::max(copy_ms, (double)f);
+        if (cudaEventElapsedTime(&f, p.mid, p.end) == cudaSuccess) copy_sum[p.dev_slot] += (double)f;
     }
+    if (rc == DISSEM_OK)
+        for (auto &kv : span) {
+            float f = 0.f;
+            cudaError_t e = cudaEventElapsedTime(&f, kv.second.first, kv.second.second);
+            if (e != cudaSuccess) {
+                rc = set_error(DISSEM_ECUDA, "cudaEventElapsedTime: %s", cudaGetErrorString(e));
+                break;
+            }
+            ms = std::max(ms, (double)f);
+            copy_ms = std::max(copy_ms, copy_sum[kv.first]);
+        }
     drop_ticket(t);
     {
         std::lock_guard<std::mutex> lk(ctx->mu);

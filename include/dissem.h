@@ -57,6 +57,12 @@ typedef int64_t dissem_sched;    /* one compiled schedule */
 /* dissem_xfer.flags: who executes the transfer.  Default (0): the GPU holding the source pushes.  PULL: the
  * destination's GPU loads from the source instead (its process needs the source layer imported). */
 #define DISSEM_XFER_PULL 1
+/* Bits 8..23 of flags: the transfer's ROUND.  Within one dissem_schedule_* call the transfers of round r start
+ * only after every transfer of round r-1 has completed on every GPU of this process (device-side event waits, no
+ * host round trip).  A relay plan (dissem_plan_relay) forwards in round r the piece that arrived in round r-1.
+ * Across processes rounds are not synchronised: submit one round per call and separate them yourself. */
+#define DISSEM_XFER_ROUND_SHIFT 8
+#define DISSEM_XFER_ROUND(r) (((r) & 0xFFFF) << DISSEM_XFER_ROUND_SHIFT)
 
 typedef struct dissem_xfer {
     int32_t src_node;
@@ -135,6 +141,15 @@ int dissem_schedule_info(dissem_ctx *ctx, dissem_sched sched, int64_t *units_out
  * are left as pushes.  gpu_of_node[i]: any id of the GPU that holds node i (e.g. the rank).  Pure host logic;
  * every process of a job computes the same answer from the same plan. */
 int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, int n_nodes);
+
+/* Relay / pipelined forwarding (generalises the reference's tee-pipe, transport.go:145-196, and mode 1's peer
+ * retransmission, node.go:1462-1484, to piece granularity).  Rewrites a plan: transfers of the same bytes from one
+ * source to k destinations become a chain  source -> d0 -> d1 -> ...  cut into `pieces` pieces (boundaries at multiples
+ * of DISSEM_CHUNK_BYTES); hop h sends piece p in round p+h, i.e. a GPU forwards a piece one round after it arrived,
+ * so the source sends every byte once and all links work at the same time.  Every other transfer is cut into the
+ * same pieces over rounds 0..pieces-1.  PULL flags are cleared (run dissem_plan_directions on the result).
+ * *out is malloc'ed: release it with dissem_free (include/dissem_host.h).  Pure host logic. */
+int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **out, int *n_out);
 
 /* Block until the batch is complete (all bytes visible at their destinations).  ms_out (may be NULL):
  * device time of the batch, max over the source GPUs involved.  The ticket is consumed. */

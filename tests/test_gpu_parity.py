@@ -445,3 +445,40 @@ def test_roles_across_gpus(mode, batched):
     r = host.run_distribution(text, mode, node_device=[i % n for i in range(4)], batched=batched, seed=SEED,
                               time_scale=1_000_000, timeout_ms=20000)
     assert r["verified"] and r["ready_equals_assignment"] and r["layers_checked"] == 6
+
+
+# ---- relay / pipelined forwarding over rounds ------------------------------------------------------
+@pytest.mark.parametrize("pieces,with_directions", [(1, False), (4, False), (7, True)])
+def test_relay_chain_over_rounds(pieces, with_directions):
+    """A layer for three destinations travels source -> d0 -> d1 -> d2 in pieces; every hop forwards what arrived one
+    round earlier.  One GPU suffices (the nodes share it); with more GPUs the hops cross NVLink."""
+    n = max(1, min(_n_gpus(), 4))
+    size = 9 * d.CHUNK_BYTES + 4096 + 48
+    devs = [i % n for i in range(4)]
+    with d.Engine(devs) as eng:
+        for layer in (0, 1, 2):
+            eng.alloc(0, layer, size)
+            eng.fill(0, layer, d.FILL_PATTERN, SEED)
+        plan = []
+        for layer in (0, 1):
+            for dst in (1, 2, 3):
+                eng.alloc(dst, layer, size)
+                eng.fill(dst, layer, d.FILL_POISON)
+                plan.append(d.Xfer(0, dst, layer, 0, 0, size, size))
+        eng.alloc(2, 2, size)
+        eng.fill(2, 2, d.FILL_POISON)
+        plan.append(d.Xfer(0, 2, 2, 0, 0, size, size))                # a plain transfer rides along, cut into the same rounds
+        xs = d.plan_relay(plan, pieces)
+        if with_directions:
+            xs = d.plan_directions(xs, devs)
+        assert sum(x.size for x in xs if x.src_node == 0 and x.layer == 0) == size
+        s = eng.compile(xs)
+        for _ in range(2):
+            eng.wait(eng.launch(s))
+        for layer, dsts in ((0, (1, 2, 3)), (1, (1, 2, 3)), (2, (2,))):
+            want = o.fill_bytes(o.FILL_PATTERN, layer, size, SEED)
+            for dst in dsts:
+                assert np.array_equal(eng.read(dst, layer), want), (layer, dst)
+                assert np.array_equal(eng.checksums(dst, layer), o.checksum(want))
+                assert eng.received(dst, layer) == 2 * size
+        eng.sched_free(s)

@@ -185,3 +185,33 @@ def test_plan_directions_heuristic():
     assert all(x.flags == 0 for x in again)
     with pytest.raises(d.DissemError):
         d.plan_directions(xs, [0, 1])
+
+
+def test_plan_relay_structure():
+    """dissem_plan_relay: every destination still receives every byte exactly once, the source sends each byte once,
+    and a hop forwards a piece exactly one round after it arrived."""
+    S = 10 * d.CHUNK_BYTES + 100
+    xs = [d.Xfer(0, 1, 5, 0, 0, S, S), d.Xfer(0, 2, 5, 0, 0, S, S), d.Xfer(0, 3, 5, 0, 0, S, S),
+          d.Xfer(2, 3, 9, 0, 0, S, S), d.Xfer(1, 0, 7, 0, 4096, 3 * d.CHUNK_BYTES, S)]
+    r = d.plan_relay(xs, 4)
+    cover = {}
+    for x in r:
+        assert x.size > 0 and x.off % d.CHUNK_BYTES == 0 or x.off == 4096
+        cover.setdefault((x.dst_node, x.layer), []).append((x.off, x.size, x.src_node, d.xfer_round(x)))
+    for (dst, layer), want in {(1, 5): (0, S), (2, 5): (0, S), (3, 5): (0, S), (3, 9): (0, S), (0, 7): (4096, 3 * d.CHUNK_BYTES)}.items():
+        pos = want[0]
+        for off, size, _src, _rnd in sorted(cover[(dst, layer)]):
+            assert off == pos
+            pos += size
+        assert pos == want[0] + want[1]
+    sent_by_source = sum(x.size for x in r if x.layer == 5 and x.src_node == 0)
+    assert sent_by_source == S                                             # once, not three times
+    # chain: the piece a node forwards in round r arrived at it in round r-1
+    arrived = {(x.dst_node, x.layer, x.off): d.xfer_round(x) for x in r}
+    for x in r:
+        if x.layer == 5 and x.src_node != 0:
+            assert arrived[(x.src_node, 5, x.off)] == d.xfer_round(x) - 1
+    assert max(d.xfer_round(x) for x in r) == 4 + 3 - 2                    # pieces + hops - 2 (rounds count from 0)
+    assert all(x.flags & d.XFER_PULL == 0 for x in r)
+    with pytest.raises(d.DissemError):
+        d.plan_relay(xs, 0)

@@ -49,7 +49,7 @@ def t_star(xfers, n, multicast):
     return max(max(e, i) for e, i in zip(eg, ing)) / (LINK_GBPS * 1e9), eg, ing
 
 
-def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, variant=1):
+def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, variant=1, relay=0):
     eng = d.Engine(list(range(n)))
     try:
         eng.set_option("variant", variant)
@@ -62,7 +62,8 @@ def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, varian
             if not eng.has(x.dst_node, x.layer):
                 eng.alloc(x.dst_node, x.layer, size)
                 eng.fill(x.dst_node, x.layer, d.FILL_POISON)
-        xs = d.plan_directions(xfers, list(range(n))) if directions else xfers
+        xs = d.plan_relay(xfers, relay) if relay else xfers
+        xs = d.plan_directions(xs, list(range(n))) if directions else xs
         s = eng.compile(xs)
         groups = eng.get_option("mcast_groups")
         for _ in range(2):
@@ -76,7 +77,7 @@ def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, varian
         D = sum(x.size for x in xfers)
         ts, eg, ing = t_star(xfers, n, multicast=(groups > 0))
         print(json.dumps({"case": name, "n_gpus": n, "layers": len(holders), "layer_bytes": size, "deliveries": len(xfers),
-                          "delivered_bytes": D, "mcast_groups": groups, "transfers_pulled": sum(1 for x in xs if x.flags & 1),
+                          "delivered_bytes": D, "mcast_groups": groups, "transfers_pulled": sum(1 for x in xs if x.flags & 1), "rounds": 1 + max(d.xfer_round(x) for x in xs),
                           "completion_ms_best": best, "completion_ms_avg": avg, "aggregate_GBps": D / best / 1e6,
                           "t_star_ms": ts * 1e3, "frac_of_link_roofline": ts * 1e3 / best, "busiest_egress": max(eg),
                           "busiest_ingress": max(ing), "verified": ok}), flush=True)
@@ -112,6 +113,11 @@ def main():
     if "mcast_reg" in cases:
         run_case(f"{tag}/NVLS multicast (register kernel)", n, holders, xfers, args.size, vmm=True, mcast=3, directions=False,
                  reps=args.reps, variant=0)
+    for c in cases:
+        if c.startswith("relay"):            # relay16, relay32p (p = with direction choice)
+            pieces = int("".join(ch for ch in c if ch.isdigit()) or 16)
+            run_case(f"{tag}/relay chains, {pieces} pieces" + (" + direction choice" if c.endswith("p") else ""), n, holders,
+                     xfers, args.size, vmm=False, mcast=0, directions=c.endswith("p"), reps=args.reps, relay=pieces)
     if "mcast_auto" in cases:
         run_case(f"{tag}/NVLS multicast + auto direction for the rest", n, holders, xfers, args.size, vmm=True, mcast=1,
                  directions=True, reps=args.reps)
