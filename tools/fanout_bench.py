@@ -75,7 +75,7 @@ def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, varian
             ok = ok and bool((eng.checksums(x.dst_node, x.layer) == ref).all() and (eng.verify(x.dst_node, x.layer) == ref).all())
         best, avg = min(times), sum(times) / len(times)
         D = sum(x.size for x in xfers)
-        ts, eg, ing = t_star(xfers, n, multicast=(groups > 0))
+        ts, eg, ing = t_star(xs if relay else xfers, n, multicast=(groups > 0))
         print(json.dumps({"case": name, "n_gpus": n, "layers": len(holders), "layer_bytes": size, "deliveries": len(xfers),
                           "delivered_bytes": D, "mcast_groups": groups, "transfers_pulled": sum(1 for x in xs if x.flags & 1), "rounds": 1 + max(d.xfer_round(x) for x in xs),
                           "completion_ms_best": best, "completion_ms_avg": avg, "aggregate_GBps": D / best / 1e6,
