@@ -482,3 +482,27 @@ def test_relay_chain_over_rounds(pieces, with_directions):
                 assert np.array_equal(eng.checksums(dst, layer), o.checksum(want))
                 assert eng.received(dst, layer) == 2 * size
         eng.sched_free(s)
+
+
+def test_config5_flow_plan_full_size_properties():
+    """BASELINE config 5: the flow.go-planned schedule (mode 3) on the ring placement at 64 MiB layers: fragments from
+    several senders tile every destination layer; fused tables equal an independent re-read and the C oracle."""
+    text = o.config_stage_ring(8, 32, o.S2)
+    cfg = o.parse_config(text)
+    p = d.plan(text, 3, time_scale=1_000_000)
+    xfers = d.parse_plan(p)
+    t, oxs, _self = o.plan_mode3(cfg, time_scale=1_000_000)
+    assert p["t"] == t and [(x.src_node, x.dst_node, x.layer, x.off, x.size) for x in xfers] == \
+        [(x.src, x.dst, x.layer, x.off, x.size) for x in oxs]
+    assert len({x.src_node for x in xfers}) > 1                       # the plan really spreads over several senders
+    with d.Engine([0] * 8) as eng:
+        _materialise(eng, cfg)
+        _alloc_destinations(eng, xfers)
+        eng.wait(eng.submit(xfers))
+        ref = {}
+        for (node, layer) in sorted({(x.dst_node, x.layer) for x in xfers}):
+            if layer not in ref:
+                ref[layer] = co.checksum(co.fill_bytes(o.FILL_PATTERN, layer, o.S2, SEED))
+            fused = eng.checksums(node, layer)
+            assert np.array_equal(fused, ref[layer]) and np.array_equal(eng.verify(node, layer), fused)
+            assert eng.received(node, layer) == o.S2
