@@ -325,6 +325,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             for (auto &it : by_dev[s]) plain[s].push_back(it.x);
         out->unit_shift = std::min(out->unit_shift, pick_unit_shift(ctx, plain));
     }
+    std::vector<std::vector<XferDesc>> part_descs;                        // parallel to out->parts
     for (size_t ri = 0; ri < assigned.size(); ++ri) {
     auto &by_dev = assigned[ri];
     for (size_t slot = 0; slot < by_dev.size(); ++slot) {
@@ -388,46 +389,104 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         part.n_descs = (int)descs.size();
         part.total_units = units;
         part.bytes = bytes;
-        CUDA_TRY(cudaSetDevice(ctx->devs[slot].dev));
-        CUDA_TRY(cudaMalloc(&part.d_descs, descs.size() * sizeof(XferDesc)));
         out->parts.push_back(part);
-        // stream-ordered upload from pageable memory: the copy is staged before the call returns
-        CUDA_TRY(cudaMemcpyAsync(part.d_descs, descs.data(), descs.size() * sizeof(XferDesc), cudaMemcpyHostToDevice,
-                                 ctx->devs[slot].stream));
+        part_descs.push_back(std::move(descs));
         out->units += units;
         out->bytes += bytes;
     }
     }   // per round
+
+    // Partially covered checksum chunks (fragment edges) may be shared by several descriptors of this schedule.  When the
+    // schedule's fragments together cover such a chunk completely, every contribution to its entry comes from this
+    // schedule, and the descriptor in the earliest round with the lowest offset owns the zeroing of the entry
+    // (kFlagZeroHead / kFlagZeroTail), which makes relaunching idempotent.  A chunk this schedule covers only in part
+    // also receives bytes from other submissions (one Transport.Send per fragment): it is left alone, its entry was
+    // zeroed when the destination buffer was allocated or reset.
+    {
+        struct Owner { int round; long long off; size_t part, desc; int flag; long long covered, length; };
+        std::map<std::pair<const void *, long long>, Owner> owners;
+        for (size_t pi = 0; pi < part_descs.size(); ++pi)
+            for (size_t di = 0; di < part_descs[pi].size(); ++di) {
+                const XferDesc &d = part_descs[pi][di];
+                if (!d.csum) continue;
+                const long long end = d.off + d.size;
+                const long long ch = d.off >> kChunkShift, ct = (end - 1) >> kChunkShift;
+                auto chunk_end = [&](long long c) { return std::min<long long>((c + 1) << kChunkShift, d.total); };
+                auto consider = [&](long long c, int flag) {
+                    const long long c0 = c << kChunkShift, c1 = chunk_end(c);
+                    const long long cov = std::min(end, c1) - std::max<long long>(d.off, c0);
+                    auto key = std::make_pair((const void *)d.csum, c);
+                    auto it = owners.find(key);
+                    if (it == owners.end()) {
+                        owners[key] = Owner{out->parts[pi].round, d.off, pi, di, flag, cov, c1 - c0};
+                    } else {
+                        it->second.covered += cov;
+                        if (std::make_pair(out->parts[pi].round, (long long)d.off) < std::make_pair(it->second.round, it->second.off)) {
+                            it->second.round = out->parts[pi].round;
+                            it->second.off = d.off;
+                            it->second.part = pi;
+                            it->second.desc = di;
+                            it->second.flag = flag;
+                        }
+                    }
+                };
+                if ((d.off & (kChunkBytes - 1)) != 0 || end < chunk_end(ch)) consider(ch, kFlagZeroHead);
+                if (ct != ch && end < chunk_end(ct)) consider(ct, kFlagZeroTail);
+            }
+        for (auto &kv : owners)
+            if (kv.second.covered == kv.second.length) part_descs[kv.second.part][kv.second.desc].flags |= kv.second.flag;
+    }
+    for (size_t pi = 0; pi < out->parts.size(); ++pi) {
+        SchedPart &part = out->parts[pi];
+        CUDA_TRY(cudaSetDevice(ctx->devs[part.dev_slot].dev));
+        CUDA_TRY(cudaMalloc(&part.d_descs, part_descs[pi].size() * sizeof(XferDesc)));
+        // stream-ordered upload from pageable memory: the copy is staged before the call returns
+        CUDA_TRY(cudaMemcpyAsync(part.d_descs, part_descs[pi].data(), part_descs[pi].size() * sizeof(XferDesc),
+                                 cudaMemcpyHostToDevice, ctx->devs[part.dev_slot].stream));
+    }
     return 0;
 }
 
 static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
-    // parts are ordered by round; a round's kernels wait (on the device, cudaStreamWaitEvent) for the end events of
-    // the previous round on every GPU of this process
-    std::vector<cudaEvent_t> prev_round, cur_round;
-    int round = s.parts.empty() ? 0 : s.parts[0].round;
-    for (auto &p : s.parts) {
-        if (p.round != round) {
-            prev_round.swap(cur_round);
-            cur_round.clear();
-            round = p.round;
+    // Parts are ordered by round.  Per round, on the device (cudaStreamWaitEvent, no host round trip):
+    //   phase A  every GPU waits for the previous round's end events, then zeroes the checksum entries it owns;
+    //   phase B  every GPU waits for the other GPUs' phase-A events of this round, then runs its copy kernel.
+    std::vector<cudaEvent_t> prev_round;
+    size_t i = 0;
+    while (i < s.parts.size()) {
+        size_t j = i;
+        while (j < s.parts.size() && s.parts[j].round == s.parts[i].round) ++j;
+        const size_t first_tp = t->parts.size();
+        for (size_t k = i; k < j; ++k) {                                  // phase A
+            const SchedPart &p = s.parts[k];
+            DeviceState &ds = ctx->devs[p.dev_slot];
+            CUDA_TRY(cudaSetDevice(ds.dev));
+            for (cudaEvent_t ev : prev_round) CUDA_TRY(cudaStreamWaitEvent(ds.stream, ev, 0));
+            TicketPart tp;
+            tp.dev_slot = p.dev_slot;
+            CUDA_TRY(cudaEventCreate(&tp.start));
+            CUDA_TRY(cudaEventCreate(&tp.mid));
+            CUDA_TRY(cudaEventCreate(&tp.end));
+            t->parts.push_back(tp);
+            CUDA_TRY(cudaEventRecord(tp.start, ds.stream));
+            CUDA_TRY(launch_zero_csum(p.d_descs, p.n_descs, ds.stream));
+            CUDA_TRY(cudaEventRecord(tp.mid, ds.stream));
         }
-        DeviceState &ds = ctx->devs[p.dev_slot];
-        CUDA_TRY(cudaSetDevice(ds.dev));
-        for (cudaEvent_t ev : prev_round) CUDA_TRY(cudaStreamWaitEvent(ds.stream, ev, 0));
-        TicketPart tp;
-        tp.dev_slot = p.dev_slot;
-        CUDA_TRY(cudaEventCreate(&tp.start));
-        CUDA_TRY(cudaEventCreate(&tp.mid));
-        CUDA_TRY(cudaEventCreate(&tp.end));
-        t->parts.push_back(tp);
-        CUDA_TRY(cudaEventRecord(tp.start, ds.stream));
-        CUDA_TRY(launch_zero_csum(p.d_descs, p.n_descs, ds.stream));
-        CUDA_TRY(cudaEventRecord(tp.mid, ds.stream));
-        LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
-        CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
-        CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
-        cur_round.push_back(tp.end);
+        std::vector<cudaEvent_t> this_round;
+        for (size_t k = i; k < j; ++k) {                                  // phase B
+            const SchedPart &p = s.parts[k];
+            DeviceState &ds = ctx->devs[p.dev_slot];
+            TicketPart &tp = t->parts[first_tp + (k - i)];
+            CUDA_TRY(cudaSetDevice(ds.dev));
+            for (size_t m = i; m < j; ++m)
+                if (m != k) CUDA_TRY(cudaStreamWaitEvent(ds.stream, t->parts[first_tp + (m - i)].mid, 0));
+            LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
+            CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
+            CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
+            this_round.push_back(tp.end);
+        }
+        prev_round.swap(this_round);
+        i = j;
     }
     return 0;
 }

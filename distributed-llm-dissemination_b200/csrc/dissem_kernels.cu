@@ -206,6 +206,23 @@ __global__ void zero_csum_kernel(const XferDesc *__restrict__ descs, int n_descs
                 else { cs[2 * c] = 0ull; cs[2 * c + 1] = 0ull; }
             }
         }
+        if (lane == 0) {
+            // partially covered chunks this descriptor owns
+            const long long ch = off >> kChunkShift, ct = (end - 1) >> kChunkShift;
+            long long che = (ch + 1) << kChunkShift, cte = (ct + 1) << kChunkShift;
+            if (che > total) che = total;
+            if (cte > total) cte = total;
+            const bool head_partial = (off & (kChunkBytes - 1)) != 0 || end < che;
+            const bool tail_partial = end < cte || ((ct << kChunkShift) < off);
+            if ((D->flags & kFlagZeroHead) && head_partial) {
+                if (mc) { st_multicast_u64(cs + 2 * ch, 0ull); st_multicast_u64(cs + 2 * ch + 1, 0ull); }
+                else { cs[2 * ch] = 0ull; cs[2 * ch + 1] = 0ull; }
+            }
+            if ((D->flags & kFlagZeroTail) && tail_partial && ct != ch) {
+                if (mc) { st_multicast_u64(cs + 2 * ct, 0ull); st_multicast_u64(cs + 2 * ct + 1, 0ull); }
+                else { cs[2 * ct] = 0ull; cs[2 * ct + 1] = 0ull; }
+            }
+        }
     }
 }
 

@@ -11,6 +11,8 @@ constexpr long long kChunkBytes = 1ll << kChunkShift;
 
 enum : int {
     kFlagMulticast = 1,   // dst / csum / received are NVLS multicast addresses (multimem.* only)
+    kFlagZeroHead = 2,    // this descriptor owns the zeroing of the partially covered chunk its fragment starts in
+    kFlagZeroTail = 4,    // ... and of the partially covered chunk it ends in
 };
 
 // One transfer as the kernels see it: bytes [off, off+size) of a layer, from the source copy to the
@@ -52,9 +54,11 @@ struct LaunchCfg {
     int tma_cfg = 0;   // TMA ring shape (stage bytes x stages, store lag): 0 16Kx6/3 (default), 1 32Kx3/1, 2 8Kx12/6, 3 16Kx4/2, 4 8Kx6/3, 5 4Kx12/6
 };
 
-// Zero the checksum entries of every chunk a descriptor covers completely (so that launching the same
-// schedule again does not accumulate onto the previous run).  Chunks shared by several fragments are
-// zeroed by their owner (dissem_layer_alloc / dissem_layer_reset).
+// Zero the checksum entries a launch is about to accumulate into (so that launching the same schedule again does
+// not add onto the previous run): every chunk a descriptor covers completely, plus the partially covered chunk at its
+// head / tail when the schedule compiler made this descriptor the chunk's owner (kFlagZeroHead / kFlagZeroTail: of the
+// fragments that share a chunk, the one in the earliest round with the lowest offset).  The engine runs all zeroing
+// of a round before any copy of that round (device-side event waits), so owners never wipe a peer's contribution.
 cudaError_t launch_zero_csum(const XferDesc *descs, int n_descs, cudaStream_t stream);
 
 // The hot kernel: copy + fused per-chunk checksum (+ completion counter) over a descriptor table.

@@ -506,3 +506,27 @@ def test_config5_flow_plan_full_size_properties():
             fused = eng.checksums(node, layer)
             assert np.array_equal(fused, ref[layer]) and np.array_equal(eng.verify(node, layer), fused)
             assert eng.received(node, layer) == o.S2
+
+
+def test_relaunching_a_fragment_plan_is_idempotent():
+    """Fragments that share checksum chunks inside ONE schedule: relaunching must not accumulate onto the shared
+    entries (the compiler names an owner that zeroes them), while fragments submitted one by one still add up."""
+    cuts = [0, 5, 262144 - 3, 262144 + 7, 600_001, 1_000_003]
+    size = cuts[-1]
+    want = o.checksum(o.fill_bytes(o.FILL_PATTERN, 11, size, SEED))
+    two = _n_gpus() >= 2
+    with d.Engine([0, 1 if two else 0, 0, 1 if two else 0]) as eng:
+        for n in (0, 1, 2):
+            eng.alloc(n, 11, size)
+            eng.fill(n, 11, d.FILL_PATTERN, SEED)
+        eng.alloc(3, 11, size)
+        frags = [(i % 3, 3, 11, a, b - a, size) for i, (a, b) in enumerate(zip(cuts, cuts[1:]))]
+        s = eng.compile(frags)
+        for k in range(3):
+            eng.wait(eng.launch(s))
+            assert np.array_equal(eng.checksums(3, 11), want), f"launch {k}"
+        eng.sched_free(s)
+        eng.reset(3, 11)
+        for f in frags:                                   # one submission per fragment (the per-message path)
+            eng.wait(eng.submit([f]))
+        assert np.array_equal(eng.checksums(3, 11), want)
