@@ -269,6 +269,7 @@ def run_ours(args, rank, world, local_rank):
         barrier()
         t1 = time.perf_counter()
         wall = t1 - t0
+        t_region0 = t0                      # (t0 is reused by the later legs)
         clock_window = "timed region"
         if clocks.summary(t0, t1)["samples"] < 3:
             # the timed region was too short for NVML (a few ms per query): keep the identical load running, outside the
@@ -419,7 +420,7 @@ def run_ours(args, rank, world, local_rank):
                     "what": "pinned host layers -> dissem_layer_write -> dissem_plan_json -> dissem_schedule_submit -> "
                             "dissem_wait -> dissem_layer_checksums"},
             "gpu_launches": launches_per_step * args.steps,
-            "clocks": dict(clocks.summary(t0, t_clk), window=clock_window),
+            "clocks": dict(clocks.summary(t_region0, t_clk), window=clock_window),
             "roofline": roof,
             "cpu_baseline": cpu,
             "verified": ok,
