@@ -179,7 +179,7 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
     auto opt_i = [&](const char *k, int64_t dflt) { const Json *v = opts.get(k); return v ? v->as_int() : dflt; };
     const NodeConf *leader_conf = cfg.Leader();
     if (!leader_conf) return set_error(DISSEM_EPLAN, "no leader found");
-    if (mode != 0 && mode != 1 && mode != 3) return set_error(DISSEM_EPLAN, "unknown or unsupported mode %d", mode);
+    if (mode < 0 || mode > 3) return set_error(DISSEM_EPLAN, "unknown mode %d", mode);            // cmd/main.go:163-164
     const uint64_t seed = (uint64_t)opt_i("seed", 0);
     const int fill = (int)opt_i("fill", DISSEM_FILL_PATTERN);
     const bool batched = opt_i("batched", 0) != 0;
@@ -221,13 +221,15 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
             switch (mode) {                                   // RunLeader, cmd/main.go:153-165
                 case 0: leader.reset(new LeaderNode(nodes.back().get(), layers, cfg.Assign)); break;
                 case 1: leader.reset(new RetransmitLeaderNode(nodes.back().get(), layers, cfg.Assign, popt)); break;
+                case 2: leader.reset(new PullRetransmitLeaderNode(nodes.back().get(), layers, cfg.Assign)); break;
                 default: leader.reset(new FlowRetransmitLeaderNode(nodes.back().get(), layers, cfg.Assign, cfg.NodeNetworkBW(), popt)); break;
             }
             leader->SetBatched(batched);
         } else {
             switch (mode) {                                   // RunReceiver, cmd/main.go:187-197
                 case 0: receivers.emplace_back(new ReceiverNode(nodes.back().get(), layers)); break;
-                case 1: receivers.emplace_back(new RetransmitReceiverNode(nodes.back().get(), layers)); break;
+                case 1:
+                case 2: receivers.emplace_back(new RetransmitReceiverNode(nodes.back().get(), layers)); break;
                 default: receivers.emplace_back(new FlowRetransmitReceiverNode(nodes.back().get(), layers)); break;
             }
         }

@@ -1,5 +1,7 @@
 #include "node.h"
 
+#include <algorithm>
+#include <cstdint>
 #include <functional>
 
 #include "../csrc/dissem_engine.h"
@@ -285,6 +287,221 @@ void RetransmitLeaderNode::sendLayers() {
             if (node_->GetTransport()->Send(x.Src, r)) Fail("couldn't send retransmit of " + std::to_string(x.Layer));
         }
     }
+}
+
+// ----------------------------------------------------------------------- PullRetransmitLeaderNode
+PullRetransmitLeaderNode::PullRetransmitLeaderNode(N *node, LayersSrc layers, Assignment assignment)
+    : RetransmitLeaderNode(node, std::move(layers), std::move(assignment), PlanOptions{}, false) {
+    Start();
+}
+
+NodeID PullRetransmitLeaderNode::getMinLoadedSender(LayerID layer) {        // caller holds mu_
+    NodeID best = 0;
+    int64_t best_rate = 0;
+    unsigned min_count = ~0u;
+    for (auto &lc : load_) {
+        auto sn = status_.find(lc.first);
+        if (sn == status_.end()) continue;
+        auto sl = sn->second.find(layer);
+        if (sl == sn->second.end()) continue;
+        const int64_t rate = sl->second.LimitRate == 0 ? INT64_MAX : sl->second.LimitRate;   // no rate limit, :962-966
+        if (rate > best_rate || (rate == best_rate && (lc.second < min_count || (lc.second == min_count && lc.first < best)))) {
+            best = lc.first;
+            best_rate = rate;
+            min_count = lc.second;
+        }
+    }
+    return best;
+}
+
+void PullRetransmitLeaderNode::sendLayers() {
+    std::vector<NodeID> dests;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        for (auto &sn : status_)
+            for (auto &sl : sn.second) owners_[sl.first].insert(sn.first);           // node.go:826-838
+        std::vector<LayerID> sorted;
+        for (auto &kv : owners_) sorted.push_back(kv.first);
+        std::stable_sort(sorted.begin(), sorted.end(), [&](LayerID a, LayerID b) {   // rarest first, ties by id, :845-851
+            if (owners_[a].size() != owners_[b].size()) return owners_[a].size() < owners_[b].size();
+            return a < b;
+        });
+        for (auto &na : assignment_)                                                 // node.go:854-867
+            for (auto &la : na.second) {
+                auto sn = status_.find(na.first);
+                bool has = false;
+                if (sn != status_.end()) {
+                    auto sl = sn->second.find(la.first);
+                    has = sl != sn->second.end() && sl->second.Location == InmemLayer;
+                }
+                if (!has) jobs_[la.first][na.first] = JobInfo{};
+            }
+        for (auto &sn : status_) load_.emplace(sn.first, 0u);                        // node.go:870-874
+        for (LayerID layer : sorted) {                                               // node.go:877-886
+            auto jl = jobs_.find(layer);
+            if (jl == jobs_.end()) continue;
+            for (auto &dj : jl->second) {
+                NodeID sender = getMinLoadedSender(layer);
+                dj.second.sender = sender;
+                dj.second.status = Pending;
+                load_[sender]++;
+            }
+        }
+        for (auto &jl : jobs_)
+            if (!owners_.count(jl.first) && err_.empty()) err_ = "mode 2: nobody holds layer " + std::to_string(jl.first);
+        for (auto &na : assignment_) dests.push_back(na.first);                      // ascending, node.go:891-896
+    }
+    {
+        Plan empty;
+        issue(empty);                        // an already satisfied assignment is ready at once (see LeaderNode::issue)
+    }
+    for (NodeID node : dests)
+        Go([this, node] {
+            if (assignNewJob(node)) Fail(std::string("failed to assign a new job: ") + last_error());
+        });
+}
+
+bool PullRetransmitLeaderNode::getRarestOwnJob(NodeID node, LayerID *layer, NodeID *dest) {   // caller holds mu_
+    size_t min_owners = ~(size_t)0;
+    bool ok = false;
+    auto sn = status_.find(node);
+    if (sn == status_.end()) return false;
+    for (auto &sl : sn->second) {
+        auto jl = jobs_.find(sl.first);
+        if (jl == jobs_.end() || jl->second.empty()) continue;
+        for (auto &dj : jl->second) {
+            if (dj.second.sender != node || dj.second.status != Pending) continue;
+            const size_t cnt = owners_[sl.first].size();
+            if (cnt < min_owners || (cnt == min_owners && sl.first < *layer)) {
+                min_owners = cnt;
+                *layer = sl.first;
+                *dest = dj.first;
+                ok = true;
+            }
+        }
+    }
+    return ok;
+}
+
+bool PullRetransmitLeaderNode::getRarestStealableJob(NodeID node, LayerID *layer, NodeID *dest, NodeID *from) {   // caller holds mu_
+    bool have = false;
+    size_t best_owners = 0;
+    int64_t best_ttf = 0;
+    auto sn = status_.find(node);
+    if (sn == status_.end()) return false;
+    for (auto &sl : sn->second) {
+        auto jl = jobs_.find(sl.first);
+        if (jl == jobs_.end()) continue;
+        const size_t owner_count = owners_[sl.first].size();
+        for (auto &dj : jl->second) {
+            const NodeID sender = dj.second.sender;
+            const int64_t sender_rate = status_[sender][sl.first].LimitRate;
+            const int64_t node_rate = sl.second.LimitRate;
+            if (sender == node || dj.second.status != Pending || load_[sender] == 0 ||
+                (node_rate != 0 && node_rate < sender_rate))                         // node.go:1038-1044
+                continue;
+            int64_t ttf;
+            auto pf = perf_.find(sender);
+            if (pf == perf_.end()) ttf = INT64_MAX;      // the sender is still stuck at its first job, :1048-1051
+            else ttf = pf->second.aveNs * (int64_t)load_[sender];
+            if (!have || owner_count < best_owners || (owner_count == best_owners && ttf > best_ttf)) {
+                have = true;
+                best_owners = owner_count;
+                best_ttf = ttf;
+                *layer = sl.first;
+                *dest = dj.first;
+                *from = sender;
+            }
+        }
+    }
+    return have;
+}
+
+int PullRetransmitLeaderNode::sendRetransmit(LayerID layer, NodeID owner, NodeID dest) {
+    {
+        std::lock_guard<std::mutex> lk(mu_);             // what was actually sent, for the run report
+        PlannedXfer x;
+        x.Src = owner;
+        x.Dest = dest;
+        x.Layer = layer;
+        const LayerMeta &om = status_[owner][layer];
+        x.DataSize = x.TotalSize = om.DataSize >= 0 ? om.DataSize : layers_[layer].DataSize;
+        plan_.Xfers.push_back(x);
+    }
+    if (owner == node_->GetMyID()) {                     // node.go:614-621
+        LayerSrc ls;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            ls = layers_[layer];
+        }
+        return SendLayerTo(dest, layer, ls, ls.DataSize);
+    }
+    auto r = std::make_shared<RetransmitMsg>();
+    r->SrcID = node_->GetMyID();
+    r->Layer = layer;
+    r->DestID = dest;
+    return node_->GetTransport()->Send(owner, r);
+}
+
+int PullRetransmitLeaderNode::assignNewJob(NodeID node) {
+    LayerID layer = 0;
+    NodeID dest = 0, from = 0;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (getRarestOwnJob(node, &layer, &dest)) {                                  // node.go:909-919
+            JobInfo &j = jobs_[layer][dest];
+            j.status = SendingRetransmit;
+            j.retransmitTime = std::chrono::steady_clock::now();
+            load_[node]--;
+        } else if (getRarestStealableJob(node, &layer, &dest, &from)) {              // node.go:922-941
+            load_[from]--;
+            JobInfo &j = jobs_[layer][dest];
+            j.sender = node;
+            j.status = SendingRetransmit;
+            j.retransmitTime = std::chrono::steady_clock::now();
+        } else {
+            return 0;                                    // "there is no job left to assign"
+        }
+    }
+    return sendRetransmit(layer, node, dest);
+}
+
+void PullRetransmitLeaderNode::handleAckMsg(const AckMsg &m) {
+    bool fire = false;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        LayerMeta meta;
+        meta.Location = m.location;
+        status_[m.SrcID][m.Layer] = meta;
+    }
+    if (!completion_[m.SrcID] && assignmentSatisfied()) {                            // node.go:752-759
+        completion_[m.SrcID] = true;
+        fire = true;
+    }
+    if (fire && !ready_.fired()) {
+        sendStartup();
+        ready_.Fire(assignment_);
+    }
+    NodeID sender;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        auto jl = jobs_.find(m.Layer);
+        if (jl == jobs_.end()) return;
+        auto dj = jl->second.find(m.SrcID);
+        if (dj == jl->second.end()) return;              // not one of our jobs (node.go:765-769)
+        sender = dj->second.sender;
+        const int64_t took = std::chrono::duration_cast<std::chrono::nanoseconds>(
+                                 std::chrono::steady_clock::now() - dj->second.retransmitTime).count();
+        Perf &pf = perf_[sender];                        // the reference's running "average", node.go:788-792, as written
+        pf.aveNs = (took + pf.aveNs) / (int64_t)(pf.completed + 1);
+        pf.completed++;
+        jl->second.erase(dj);                            // node.go:797
+    }
+    // the sender is idle again: hand it its next job.  (assignNewJob may block in a layer send when the sender is the
+    // leader itself, so it runs off the dispatcher as the reference's `go handleAckMsg` does.)
+    Go([this, sender] {
+        if (assignNewJob(sender)) Fail(std::string("failed to assign a new job after an ack: ") + last_error());
+    });
 }
 
 // ----------------------------------------------------------------------- FlowRetransmitLeaderNode

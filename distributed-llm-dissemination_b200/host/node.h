@@ -121,7 +121,7 @@ protected:
     void handleAnnounceMsg(const AnnounceMsg &m);          // node.go:295-324
     virtual Plan makePlan();                               // mode 0: node.go:326-352
     virtual void sendLayers();                             // issues the plan
-    void handleAckMsg(const AckMsg &m);                    // node.go:410-432
+    virtual void handleAckMsg(const AckMsg &m);            // node.go:410-432
     void handleLayerMsg(const LayerMsg &m);                // node.go:376-407
     bool assignmentSatisfied();                            // node.go:435-446
     void sendStartup();                                    // node.go:456-469
@@ -144,6 +144,37 @@ protected:
     Plan makePlan() override;
     void sendLayers() override;       // leader-owned layers are sent by the leader, others by retransmitMsg (:611-626)
     PlanOptions opt_;
+};
+
+// mode 2: PullRetransmitLeaderNode, node.go:628-1073 — pull-based work conservation: every sender has at most one
+// job in flight; when the destination acks it, the sender is handed its next own job (rarest layer first) or steals a
+// pending job of the sender expected to finish last.
+class PullRetransmitLeaderNode : public RetransmitLeaderNode {
+public:
+    PullRetransmitLeaderNode(N *node, LayersSrc layers, Assignment assignment);   // NewPullRetransmitLeaderNode, node.go:674
+
+protected:
+    void sendLayers() override;                            // node.go:810-901
+    void handleAckMsg(const AckMsg &m) override;           // node.go:741-807
+    int assignNewJob(NodeID node);                         // node.go:906-945
+
+private:
+    enum JobStatus { Pending = 0, SendingRetransmit = 1 };                        // node.go:631-638
+    struct JobInfo {                                       // node.go:640-645
+        NodeID sender = 0;
+        JobStatus status = Pending;
+        std::chrono::steady_clock::time_point retransmitTime;
+    };
+    struct Perf { int64_t aveNs = 0; unsigned completed = 0; };                   // nodePerformance, node.go:657-660
+    bool getRarestOwnJob(NodeID node, LayerID *layer, NodeID *dest);              // node.go:980-1010
+    bool getRarestStealableJob(NodeID node, LayerID *layer, NodeID *dest, NodeID *from);   // node.go:1012-1073
+    NodeID getMinLoadedSender(LayerID layer);              // node.go:948-978
+    int sendRetransmit(LayerID layer, NodeID owner, NodeID dest);                 // node.go:611-626
+    std::map<LayerID, std::map<NodeID, JobInfo>> jobs_;    // jobsInfoMap
+    std::map<NodeID, unsigned> load_;                      // senderLoadCounter
+    std::map<NodeID, Perf> perf_;
+    std::map<LayerID, NodeIDs> owners_;                    // layerOwners
+    std::map<NodeID, bool> completion_;                    // nodeCompletionStatus
 };
 
 // mode 3: FlowRetransmitLeaderNode, node.go:1075-1288

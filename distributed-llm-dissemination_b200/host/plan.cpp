@@ -1,6 +1,7 @@
 #include "plan.h"
 
 #include <algorithm>
+#include <cstdint>
 
 namespace dissem {
 namespace host {
@@ -150,13 +151,72 @@ Plan PlanMode3(NodeID leader, const LayersSrc &leader_layers, const Status &stat
     return p;
 }
 
+Plan PlanMode2Initial(NodeID leader, const LayersSrc &leader_layers, const Status &status, const Assignment &a) {
+    (void)leader;
+    std::map<LayerID, std::vector<NodeID>> owners;                    // node.go:826-838
+    for (auto &sn : status)
+        for (auto &sl : sn.second) owners[sl.first].push_back(sn.first);
+    std::vector<LayerID> sorted;                                      // node.go:841-851
+    for (auto &kv : owners) sorted.push_back(kv.first);
+    std::stable_sort(sorted.begin(), sorted.end(), [&](LayerID x, LayerID y) {
+        if (owners[x].size() != owners[y].size()) return owners[x].size() < owners[y].size();
+        return x < y;
+    });
+    std::map<LayerID, std::vector<NodeID>> jobs;                      // node.go:854-867: (layer -> dests still lacking it in memory)
+    for (auto &na : a)
+        for (auto &la : na.second) {
+            auto sn = status.find(na.first);
+            bool has = false;
+            if (sn != status.end()) {
+                auto sl = sn->second.find(la.first);
+                has = sl != sn->second.end() && sl->second.Location == InmemLayer;
+            }
+            if (!has) jobs[la.first].push_back(na.first);
+        }
+    std::map<NodeID, unsigned> load;                                  // node.go:870-874
+    for (auto &sn : status) load[sn.first] = 0;
+    Plan p;
+    for (LayerID layer : sorted) {
+        auto jl = jobs.find(layer);
+        if (jl == jobs.end()) continue;
+        for (NodeID dest : jl->second) {                              // Go: map order; ascending here
+            NodeID best = 0;                                          // getMinLoadedSender, node.go:948-978
+            int64_t best_rate = 0;
+            unsigned min_count = ~0u;
+            for (auto &lc : load) {
+                auto sn = status.find(lc.first);
+                auto sl = sn->second.find(layer);
+                if (sl == sn->second.end()) continue;
+                int64_t rate = sl->second.LimitRate == 0 ? INT64_MAX : sl->second.LimitRate;
+                if (rate > best_rate || (rate == best_rate && (lc.second < min_count || (lc.second == min_count && lc.first < best)))) {
+                    best = lc.first;
+                    best_rate = rate;
+                    min_count = lc.second;
+                }
+            }
+            load[best]++;
+            PlannedXfer x;
+            x.Src = best;
+            x.Dest = dest;
+            x.Layer = layer;
+            const LayerMeta &om = status.at(best).at(layer);
+            auto ll = leader_layers.find(layer);
+            x.DataSize = x.TotalSize = om.DataSize >= 0 ? om.DataSize : (ll != leader_layers.end() ? ll->second.DataSize : 0);
+            p.Xfers.push_back(x);
+        }
+    }
+    for (auto &jl : jobs)
+        if (!owners.count(jl.first)) throw PlanError("mode 2: nobody holds layer " + std::to_string(jl.first));
+    return p;
+}
+
 Plan MakePlan(int mode, NodeID leader, const LayersSrc &leader_layers, const Status &status, const Assignment &a,
               const std::map<NodeID, int64_t> &network_bw, const PlanOptions &opt) {
     switch (mode) {                                       // cmd/main.go:153-165
         case 0: return PlanMode0(leader, leader_layers, status, a);
         case 1: return PlanMode1(leader, leader_layers, status, a, opt);
         case 3: return PlanMode3(leader, leader_layers, status, a, network_bw, opt);
-        case 2: throw PlanError("mode 2 (pull / work stealing, node.go:628-1073) is outside this engine's scope");
+        case 2: return PlanMode2Initial(leader, leader_layers, status, a);
         default: throw PlanError("unknown mode");         // cmd/main.go:163-164
     }
 }

@@ -42,6 +42,11 @@ Plan PlanMode1(NodeID leader, const LayersSrc &leader_layers, const Status &stat
                const PlanOptions &opt);
 Plan PlanMode3(NodeID leader, const LayersSrc &leader_layers, const Status &status, const Assignment &a,
                const std::map<NodeID, int64_t> &network_bw, const PlanOptions &opt);
+// mode 2, the deterministic part: PullRetransmitLeaderNode.sendLayers' initial job table (node.go:810-886) — layers
+// taken rarest first (fewest owners, ties by id), each (layer, dest) job given to getMinLoadedSender (node.go:948-978:
+// highest LimitRate, 0 = unlimited; ties by fewest jobs so far, then lowest id).  Which jobs are later STOLEN depends on
+// measured completion times (node.go:980-1073) and is decided at run time by the role (node.cpp).
+Plan PlanMode2Initial(NodeID leader, const LayersSrc &leader_layers, const Status &status, const Assignment &a);
 Plan MakePlan(int mode, NodeID leader, const LayersSrc &leader_layers, const Status &status, const Assignment &a,
               const std::map<NodeID, int64_t> &network_bw, const PlanOptions &opt);
 

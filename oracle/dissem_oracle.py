@@ -334,6 +334,42 @@ def plan_mode1(cfg: Config, seed: int = 0, policy: str = "random") -> List[Xfer]
     return out
 
 
+def plan_mode2_initial(cfg: Config) -> List[Xfer]:
+    """PullRetransmitLeaderNode.sendLayers' initial job table, node.go:810-886 with getMinLoadedSender :948-978.
+    (Which jobs are stolen later depends on measured times, node.go:980-1073; any owner is then a valid sender.)"""
+    st = {n.id: dict(n.layers) for n in cfg.nodes}
+    owners: Dict[int, List[int]] = {}
+    for node in sorted(st):
+        for layer in st[node]:
+            owners.setdefault(layer, []).append(node)
+    sorted_layers = sorted(owners, key=lambda l: (len(owners[l]), l))                 # rarest first, :841-851
+    jobs: Dict[int, List[int]] = {}
+    for node in sorted(cfg.assignment):
+        for layer in cfg.assignment[node]:
+            if layer not in st.get(node, {}):                                          # :858 (all layers are in memory here)
+                jobs.setdefault(layer, []).append(node)
+    for layer in jobs:
+        if layer not in owners:
+            raise ValueError(f"mode 2: nobody holds layer {layer}")
+    load = {n: 0 for n in sorted(st)}
+    out = []
+    for layer in sorted_layers:
+        for dest in jobs.get(layer, []):
+            best, best_rate, min_count = 0, 0, None
+            for sender in sorted(load):
+                if layer not in st[sender]:
+                    continue
+                rate = limit_rate(cfg.node(sender), layer) or INT64_MAX                # 0 = no limit, :962-966
+                cnt = load[sender]
+                if rate > best_rate or (rate == best_rate and (min_count is None or cnt < min_count or
+                                                               (cnt == min_count and sender < best))):
+                    best, best_rate, min_count = sender, rate, cnt
+            load[best] += 1
+            size = cfg.node(best).layers[layer][0]
+            out.append(Xfer(best, dest, layer, 0, size, size))
+    return out
+
+
 # ---- mode 3: flow.go ------------------------------------------------------------------
 K_SOURCE, K_SENDER, K_CLIENT, K_LAYER, K_RECEIVER, K_SINK = range(6)   # flow.go:14-21
 

@@ -131,8 +131,6 @@ def test_bad_inputs_fail_loudly():
         d.plan(json.dumps({"Nodes": [{"Id": 0}], "Assignment": {}}), 0)
     assert e.value.code == -10 and "no leader" in str(e.value)
     with pytest.raises(d.DissemError):
-        d.plan(o.config_readme(), 2)
-    with pytest.raises(d.DissemError):
         d.plan(o.config_readme(), 7)                            # "unknown mode", cmd/main.go:163-164
 
 
@@ -215,3 +213,22 @@ def test_plan_relay_structure():
     assert all(x.flags & d.XFER_PULL == 0 for x in r)
     with pytest.raises(d.DissemError):
         d.plan_relay(xs, 0)
+
+
+@pytest.mark.parametrize("name", sorted(CONFIGS))
+def test_mode2_initial_jobs_match_oracle(name):
+    """PullRetransmitLeaderNode's initial job table (node.go:810-886): rarest layer first, least-loaded owner."""
+    text = CONFIGS[name]()
+    got = _rows(d.plan(text, 2))
+    assert got == _orows(o.plan_mode2_initial(o.parse_config(text)))
+    cand = o.mode1_owner_candidates(o.parse_config(text))
+    assert len(got) == len(cand)
+    for (s, dst, l, *_r) in got:
+        assert s in cand[(dst, l)]
+
+
+def test_mode2_ring_fixture_known_answer():
+    """node_test.go:246-272 (tcp_pullretransmission) on the ring placement: every needed layer has owners {leader, one
+    peer}; all loads start at 0, so ties go to the lowest id (node.go:967-971): layer 1 -> leader, then the peers."""
+    got = _rows(d.plan(o.config_ring_fixture(), 2))
+    assert got == [(0, 1, 1, 0, 1, 1), (3, 2, 2, 0, 1, 1), (4, 3, 3, 0, 1, 1), (1, 4, 4, 0, 1, 1)]
