@@ -9,7 +9,7 @@ from typing import List, Optional, Sequence
 from ._capi import DissemError, Xfer, lib
 
 POLICY_RANDOM, POLICY_BALANCED = 0, 1
-PLAN_ZERO_RATE_UNLIMITED, PLAN_SIZES_FROM_ANNOUNCES = 1, 2
+PLAN_ZERO_RATE_UNLIMITED, PLAN_SIZES_FROM_ANNOUNCES, PLAN_MULTI_DEST = 1, 2, 4
 
 
 class HostError(DissemError):

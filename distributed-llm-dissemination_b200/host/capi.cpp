@@ -28,6 +28,7 @@ static PlanOptions make_opts(uint64_t seed, int policy, int64_t time_scale, int 
     o.Flow.TimeScale = time_scale > 0 ? time_scale : 1;
     o.Flow.ZeroRateUnlimited = (flags & DISSEM_PLAN_ZERO_RATE_UNLIMITED) != 0;
     o.SizesFromAnnounces = (flags & DISSEM_PLAN_SIZES_FROM_ANNOUNCES) != 0;
+    o.Flow.PerDestLayers = (flags & DISSEM_PLAN_MULTI_DEST) != 0;
     return o;
 }
 

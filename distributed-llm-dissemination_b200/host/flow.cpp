@@ -10,13 +10,19 @@ namespace host {
 
 static constexpr int64_t kInf = std::numeric_limits<int64_t>::max();   // math.MaxInt64, flow.go:252
 
+std::vector<std::pair<LayerID, NodeID>> FlowGraph::layer_vertices(LayerID l) const {
+    std::vector<std::pair<LayerID, NodeID>> v;
+    for (auto it = layer_idx_.lower_bound({l, 0}); it != layer_idx_.end() && it->first.first == l; ++it) v.push_back(it->first);
+    return v;
+}
+
 FlowGraph::FlowGraph(const Status &status, const std::map<LayerID, int64_t> &sizes,
                      const std::map<NodeID, int64_t> &network_bw, const Assignment &assignment, FlowOptions opt)
     : status_(status), sizes_(sizes), bw_(network_bw), assignment_(assignment), opt_(opt) {
     if (opt_.TimeScale <= 0) throw std::invalid_argument("TimeScale must be positive");
-    std::set<LayerID> need;
+    std::set<std::pair<LayerID, NodeID>> need;
     for (auto &a : assignment_)
-        for (auto &l : a.second) need.insert(l.first);
+        for (auto &l : a.second) need.insert({l.first, opt_.PerDestLayers ? a.first : kAnyDest});
     needed_.assign(need.begin(), need.end());
     // vertex numbering = addIndex order of flow.go:79-122
     int n = 0;
@@ -27,7 +33,7 @@ FlowGraph::FlowGraph(const Status &status, const std::map<LayerID, int64_t> &siz
         for (auto &l : s.second) kinds.insert((int)l.second.Source);
         for (int k : kinds) client_idx_[{s.first, k}] = n++;
     }
-    for (LayerID l : needed_) layer_idx_[l] = n++;
+    for (auto &v : needed_) layer_idx_[v] = n++;
     for (auto &a : assignment_) receiver_idx_[a.first] = n++;
     sink_ = n++;
     n_ = n;
@@ -38,15 +44,16 @@ FlowGraph::FlowGraph(const Status &status, const std::map<LayerID, int64_t> &siz
     for (auto &s : status_) {
         link(src_, sender_idx_[s.first]);
         for (auto &l : s.second) {
-            if (!need.count(l.first)) continue;
+            auto vs = layer_vertices(l.first);
+            if (vs.empty()) continue;
             int c = client_idx_[{s.first, (int)l.second.Source}];
             link(sender_idx_[s.first], c);
-            link(c, layer_idx_[l.first]);
+            for (auto &v : vs) link(c, layer_idx_[v]);
         }
     }
     for (auto &a : assignment_) {
         int r = receiver_idx_[a.first];
-        for (auto &l : a.second) link(layer_idx_[l.first], r);
+        for (auto &l : a.second) link(layer_idx_[{l.first, opt_.PerDestLayers ? a.first : kAnyDest}], r);
         link(r, sink_);
     }
     nbr_.resize(n_);
@@ -67,17 +74,18 @@ void FlowGraph::BuildEdgeCapacity(int64_t t) {
         auto bw = bw_.find(s.first);
         C(src_, sender_idx_[s.first]) = Cap(bw == bw_.end() ? 0 : bw->second, t);
         for (auto &l : s.second) {      // ascending layer id: "last write wins" made deterministic
-            if (!layer_idx_.count(l.first)) continue;
+            auto vs = layer_vertices(l.first);
+            if (vs.empty()) continue;
             int c = client_idx_[{s.first, (int)l.second.Source}];
             C(sender_idx_[s.first], c) = (l.second.LimitRate == 0 && opt_.ZeroRateUnlimited) ? kInf : Cap(l.second.LimitRate, t);
-            C(c, layer_idx_[l.first]) = kInf;
+            for (auto &v : vs) C(c, layer_idx_[v]) = kInf;
         }
     }
     for (auto &a : assignment_) {
         int r = receiver_idx_[a.first];
         for (auto &l : a.second) {
             auto sz = sizes_.find(l.first);
-            C(layer_idx_[l.first], r) = sz == sizes_.end() ? 0 : sz->second;
+            C(layer_idx_[{l.first, opt_.PerDestLayers ? a.first : kAnyDest}], r) = sz == sizes_.end() ? 0 : sz->second;
         }
         auto bw = bw_.find(a.first);
         C(r, sink_) = Cap(bw == bw_.end() ? 0 : bw->second, t);
@@ -122,8 +130,8 @@ int64_t FlowGraph::UpdateMaxFlow(int64_t t) {
 
 int64_t FlowGraph::GetJobAssignment(std::vector<FlowJobInfo> *jobs) {
     int64_t required = 0;
-    for (LayerID l : needed_) {                       // each distinct layer once, flow.go:150-152
-        auto sz = sizes_.find(l);
+    for (auto &v : needed_) {                         // each distinct layer once, flow.go:150-152 (per pair when extended)
+        auto sz = sizes_.find(v.first);
         required += sz == sizes_.end() ? 0 : sz->second;
     }
     int64_t upper = 1;
@@ -140,23 +148,23 @@ int64_t FlowGraph::GetJobAssignment(std::vector<FlowJobInfo> *jobs) {
     }
     UpdateMaxFlow(best);                              // flow.go:191
     jobs->clear();
-    std::map<LayerID, int64_t> offset;
+    std::map<std::pair<LayerID, NodeID>, int64_t> offset;
     for (auto &s : status_)                           // Go iterates this map in random order (:197); ascending here
-        for (auto &l : s.second) {
-            auto li = layer_idx_.find(l.first);
-            if (li == layer_idx_.end()) continue;
-            int c = client_idx_[{s.first, (int)l.second.Source}];
-            int64_t flow = cap_[(size_t)li->second * n_ + c];     // reverse residual edge layer -> source, :205
-            if (flow > 0) {
-                FlowJobInfo j;
-                j.SenderID = s.first;
-                j.Layer = l.first;
-                j.DataSize = flow;
-                j.Offset = offset[l.first];
-                offset[l.first] += flow;
-                jobs->push_back(j);
+        for (auto &l : s.second)
+            for (auto &v : layer_vertices(l.first)) {
+                int c = client_idx_[{s.first, (int)l.second.Source}];
+                int64_t flow = cap_[(size_t)layer_idx_[v] * n_ + c];   // reverse residual edge layer -> source, :205
+                if (flow > 0) {
+                    FlowJobInfo j;
+                    j.SenderID = s.first;
+                    j.Layer = l.first;
+                    j.DataSize = flow;
+                    j.Offset = offset[v];
+                    j.Dest = v.second;
+                    offset[v] += flow;
+                    jobs->push_back(j);
+                }
             }
-        }
     return best;
 }
 

@@ -15,16 +15,23 @@
 namespace dissem {
 namespace host {
 
+constexpr NodeID kAnyDest = 0xFFFFFFFFu;
+
 struct FlowJobInfo {          // flowJobInfo, flow.go:30-35
     NodeID SenderID = 0;
     LayerID Layer = 0;
     int64_t DataSize = 0;
     int64_t Offset = 0;
+    NodeID Dest = kAnyDest;   // set only by the per-destination extension (FlowOptions::PerDestLayers)
 };
 
 struct FlowOptions {
     int64_t TimeScale = 1;            // planner ticks per second; 1 = the reference's integer seconds
     bool ZeroRateUnlimited = false;   // treat LimitRate == 0 as "no cap" (the reference would never terminate)
+    // Extension (the reference accepts ONE destination per layer, node.go:1078, and counts each distinct layer once in
+    // the required flow, flow.go:150-152): one layer vertex per (layer, destination) pair, demand = sum over pairs,
+    // fragments and offsets per pair.  With one destination per layer the graph, and hence the plan, is unchanged.
+    bool PerDestLayers = false;
 };
 
 class FlowGraph {
@@ -49,11 +56,12 @@ private:
     std::map<NodeID, int64_t> bw_;
     Assignment assignment_;
     FlowOptions opt_;
-    std::vector<LayerID> needed_;
+    std::vector<std::pair<LayerID, NodeID>> needed_;     // layer vertices: (layer, kAnyDest) or (layer, dest)
     int n_ = 0, src_ = 0, sink_ = 0;
     std::map<NodeID, int> sender_idx_, receiver_idx_;
     std::map<std::pair<NodeID, int>, int> client_idx_;
-    std::map<LayerID, int> layer_idx_;
+    std::map<std::pair<LayerID, NodeID>, int> layer_idx_;
+    std::vector<std::pair<LayerID, NodeID>> layer_vertices(LayerID l) const;
     std::vector<int64_t> cap_;                     // residual capacities, n x n
     std::vector<std::vector<int>> nbr_;            // ascending neighbour lists (either direction)
 };

@@ -140,7 +140,7 @@ Plan PlanMode3(NodeID leader, const LayersSrc &leader_layers, const Status &stat
     for (auto &j : jobs) {                                // dispatchJob, node.go:1264-1288
         PlannedXfer x;
         x.Src = j.SenderID;
-        x.Dest = layer_dest[j.Layer];
+        x.Dest = j.Dest != kAnyDest ? j.Dest : layer_dest[j.Layer];
         x.Layer = j.Layer;
         x.Offset = j.Offset;
         x.DataSize = j.DataSize;

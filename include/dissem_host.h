@@ -22,6 +22,8 @@ extern "C" {
 
 #define DISSEM_PLAN_ZERO_RATE_UNLIMITED 1 /* mode 3: LimitRate == 0 means "no cap" */
 #define DISSEM_PLAN_SIZES_FROM_ANNOUNCES 2 /* mode 3: sizes of layers the leader lacks come from announces */
+#define DISSEM_PLAN_MULTI_DEST 4 /* mode 3: one demand per (layer, destination) pair instead of the reference's one
+                                    destination per layer (node.go:1078); unchanged plan when every layer has one */
 
 /* Parse the reference's config JSON (cmd/config.go:14-45; nested or README-flat schema) and produce the plan
  * the leader of `mode` (cmd/main.go:153-165: 0 LeaderNode, 1 RetransmitLeaderNode, 3 FlowRetransmitLeaderNode)

@@ -382,7 +382,7 @@ class FlowGraph:
 
     def __init__(self, status_meta: Dict[int, Dict[int, Tuple[int, int]]], layer_sizes: Dict[int, int],
                  network_bw: Dict[int, int], assignment: Dict[int, List[int]], time_scale: int = 1,
-                 zero_rate_unlimited: bool = False):
+                 zero_rate_unlimited: bool = False, per_dest: bool = False):
         # status_meta: node -> {layer: (LimitRate, SourceType)}
         self.status = status_meta
         self.sizes = layer_sizes
@@ -390,7 +390,11 @@ class FlowGraph:
         self.assignment = assignment
         self.time_scale = time_scale
         self.zero_rate_unlimited = zero_rate_unlimited
+        # per_dest (this repo's extension; the reference has ONE destination per layer, node.go:1078): a layer vertex per
+        # (layer, destination) pair.  Otherwise one vertex per layer, keyed (layer, None).
+        self.per_dest = per_dest
         self.assignment_layers = sorted({l for ls in assignment.values() for l in ls})   # flow.go:57-65
+        self.layer_vertices = sorted({(l, (n if per_dest else -1)) for n, ls in assignment.items() for l in ls})
         idx = {}
 
         def add(key):
@@ -402,8 +406,8 @@ class FlowGraph:
         for n in sorted(status_meta):                                   # flow.go:91-107
             for stype in sorted({m[1] for m in status_meta[n].values()}):
                 add((K_CLIENT, n, stype))
-        for l in self.assignment_layers:                                # flow.go:110-113
-            add((K_LAYER, l))
+        for (l, dst) in self.layer_vertices:                            # flow.go:110-113
+            add((K_LAYER, l, dst))
         for n in sorted(assignment):                                    # flow.go:116-119
             add((K_RECEIVER, n))
         add((K_SINK,))                                                  # flow.go:122
@@ -431,12 +435,14 @@ class FlowGraph:
                 c = self.idx[(K_CLIENT, n, stype)]
                 cap = INT64_MAX if (rate == 0 and self.zero_rate_unlimited) else self._cap(rate, t)
                 self.adj[self.idx[(K_SENDER, n)], c] = cap
-                self.adj[c, self.idx[(K_LAYER, layer)]] = INT64_MAX     # flow.go:252
+                for (l2, dst) in self.layer_vertices:
+                    if l2 == layer:
+                        self.adj[c, self.idx[(K_LAYER, layer, dst)]] = INT64_MAX     # flow.go:252
         sink = self.idx[(K_SINK,)]
         for n, layers in self.assignment.items():
             r = self.idx[(K_RECEIVER, n)]
             for layer in layers:
-                self.adj[self.idx[(K_LAYER, layer)], r] = self.sizes[layer]   # flow.go:261
+                self.adj[self.idx[(K_LAYER, layer, n if self.per_dest else -1)], r] = self.sizes[layer]   # flow.go:261
             self.adj[r, sink] = self._cap(self.bw.get(n, 0), t)         # flow.go:267
 
     def bfs(self, src: int, dest: int):                                 # flow.go:283-315
@@ -480,7 +486,7 @@ class FlowGraph:
                 v = p
 
     def get_job_assignment(self):                                       # flow.go:146-219
-        required = sum(self.sizes[l] for l in self.assignment_layers)   # each distinct layer once, :150-152
+        required = sum(self.sizes[l] for (l, _d) in self.layer_vertices)   # each distinct layer once, :150-152 (per pair if extended)
         t_upper = 1
         while True:
             if self.update_max_flow(t_upper) >= required:
@@ -498,23 +504,26 @@ class FlowGraph:
                 hi = m - 1
         self.update_max_flow(t)                                         # flow.go:191
         jobs = []
-        offset: Dict[int, int] = {}
+        offset: Dict[Tuple[int, int], int] = {}
         needed = set(self.assignment_layers)
         for sender in sorted(self.status):                              # Go: map order (:197); we fix ascending
             for layer in sorted(self.status[sender]):
                 if layer not in needed:
                     continue
                 _, stype = self.status[sender][layer]
-                flow = int(self.adj[self.idx[(K_LAYER, layer)], self.idx[(K_CLIENT, sender, stype)]])
-                if flow > 0:                                            # reverse residual edge, :205-210
-                    off = offset.get(layer, 0)
-                    jobs.append((sender, layer, flow, off))
-                    offset[layer] = off + flow
+                for (l2, dst) in self.layer_vertices:
+                    if l2 != layer:
+                        continue
+                    flow = int(self.adj[self.idx[(K_LAYER, layer, dst)], self.idx[(K_CLIENT, sender, stype)]])
+                    if flow > 0:                                        # reverse residual edge, :205-210
+                        off = offset.get((layer, dst), 0)
+                        jobs.append((sender, layer, flow, off, dst))
+                        offset[(layer, dst)] = off + flow
         return t, jobs
 
 
 def plan_mode3(cfg: Config, time_scale: int = 1, zero_rate_unlimited: bool = False,
-               sizes_from_announces: bool = False):
+               sizes_from_announces: bool = False, multi_dest: bool = False):
     """FlowRetransmitLeaderNode.assignJobs + sendLayers + dispatchJob, node.go:1200-1288.
     Returns (t, xfers, self_jobs).  `time_scale` = planner ticks per second (1 = the reference's
     integer seconds; NVLink-speed configs need 10^6 or t is always 1 and the plan degenerates).
@@ -546,9 +555,9 @@ def plan_mode3(cfg: Config, time_scale: int = 1, zero_rate_unlimited: bool = Fal
             if l not in sizes:
                 raise ValueError(f"mode 3: leader does not know the size of layer {l} (flow.go:151)")
     g = FlowGraph(st_meta, sizes, {n.id: n.network_bw for n in cfg.nodes}, modified, time_scale,
-                  zero_rate_unlimited)
+                  zero_rate_unlimited, per_dest=multi_dest)
     t, jobs = g.get_job_assignment()
-    xfers = [Xfer(s, layer_dest[l], l, off, size, sizes[l]) for (s, l, size, off) in jobs]
+    xfers = [Xfer(s, (dst if multi_dest else layer_dest[l]), l, off, size, sizes[l]) for (s, l, size, off, dst) in jobs]
     return t, xfers, self_jobs
 
 

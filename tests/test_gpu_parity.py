@@ -532,3 +532,42 @@ def test_relaunching_a_fragment_plan_is_idempotent():
         for f in frags:                                   # one submission per fragment (the per-message path)
             eng.wait(eng.submit([f]))
         assert np.array_equal(eng.checksums(3, 11), want)
+
+
+def test_mode3_multi_destination_plan_delivers():
+    """The per-(layer, destination) flow plan on the fan-out placement: fragments from the holder tile every copy."""
+    size = 3 * (1 << 20) + 4096
+    text = o.config_fanout(n_nodes=8, n_layers=24, size=size)
+    cfg = o.parse_config(text)
+    xfers = d.parse_plan(d.plan(text, 3, time_scale=1_000_000, flags=host.PLAN_SIZES_FROM_ANNOUNCES | host.PLAN_MULTI_DEST))
+    n = max(1, min(_n_gpus(), 8))
+    with d.Engine([i % n for i in range(8)]) as eng:
+        _materialise(eng, cfg)
+        _alloc_destinations(eng, xfers)
+        s = eng.compile(xfers)
+        for _ in range(2):
+            eng.wait(eng.launch(s))
+        for node, layers in cfg.assignment.items():
+            for layer in layers:
+                want = o.fill_bytes(o.FILL_PATTERN, layer, size, SEED)
+                assert np.array_equal(eng.read(node, layer), want), (node, layer)
+                assert np.array_equal(eng.checksums(node, layer), o.checksum(want))
+
+
+def test_cli_keeps_the_reference_surface():
+    """cmd/main.go:26-31 (usage when -id / -f are missing) and :168 (`Time to deliver:`)."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "distributed-llm-dissemination_b200", "dissem")
+    if not os.path.exists(exe):
+        pytest.skip("CLI not built")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
+    assert out.startswith("usage: -id 0 -f config.json -s . -m 2 -l -v")
+    cfg = os.path.join(root, "tests", "data", "cli_config_4x8.json")
+    for mode in ("0", "1", "2", "3"):
+        r = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", mode, "-v"], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stderr
+        assert "launching leader..." in r.stdout and "Time to deliver: " in r.stdout
+        assert '"verified":true' in r.stdout and '"ready_equals_assignment":true' in r.stdout
+    bad = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", "9"], capture_output=True, text=True, timeout=60)
+    assert bad.returncode != 0 and "unknown mode" in bad.stderr

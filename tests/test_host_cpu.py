@@ -232,3 +232,30 @@ def test_mode2_ring_fixture_known_answer():
     peer}; all loads start at 0, so ties go to the lowest id (node.go:967-971): layer 1 -> leader, then the peers."""
     got = _rows(d.plan(o.config_ring_fixture(), 2))
     assert got == [(0, 1, 1, 0, 1, 1), (3, 2, 2, 0, 1, 1), (4, 3, 3, 0, 1, 1), (1, 4, 4, 0, 1, 1)]
+
+
+def test_mode3_multi_destination_extension():
+    """Per-(layer, destination) demand (the reference allows one destination per layer, node.go:1078): every
+    destination's fragments tile its copy of the layer; C++ == oracle; single-destination plans are unchanged."""
+    text = o.config_fanout(n_nodes=8, n_layers=24, size=3 * (1 << 20) + 4096)
+    flags = host.PLAN_SIZES_FROM_ANNOUNCES | host.PLAN_MULTI_DEST
+    p = d.plan(text, 3, time_scale=1_000_000, flags=flags)
+    cfg = o.parse_config(text)
+    t, xs, _self = o.plan_mode3(cfg, time_scale=1_000_000, sizes_from_announces=True, multi_dest=True)
+    assert p["t"] == t and _rows(p) == _orows(xs)
+    need = {(n, l) for n, ls in cfg.assignment.items() for l in ls}
+    got = {}
+    for (s, dst, l, off, size, total) in _rows(p):
+        got.setdefault((dst, l), []).append((off, size))
+        assert l in cfg.node(s).layers
+    assert set(got) == need
+    for key, frs in got.items():
+        pos = 0
+        for off, size in sorted(frs):
+            assert off == pos
+            pos += size
+        assert pos == 3 * (1 << 20) + 4096
+    # one destination per layer: the extension changes nothing
+    text1 = o.config_stage_ring(8, 32, o.S2)
+    assert _rows(d.plan(text1, 3, time_scale=1_000_000, flags=host.PLAN_MULTI_DEST)) == _rows(d.plan(text1, 3, time_scale=1_000_000))
+    assert _rows(d.plan(o.config_conf_json(), 3, flags=host.PLAN_MULTI_DEST)) == _rows(d.plan(o.config_conf_json(), 3))
