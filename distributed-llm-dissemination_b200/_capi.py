@@ -64,6 +64,7 @@ def load_library() -> ctypes.CDLL:
         "dissem_layer_read": (c.c_int, [P, c.c_int, c.c_int, P, i64, i64]),
         "dissem_host_alloc": (c.c_int, [c.POINTER(P), i64]),
         "dissem_host_free": (c.c_int, [P]),
+        "dissem_layer_attach_host": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
         "dissem_layer_export": (c.c_int, [P, c.c_int, c.c_int, P]),
         "dissem_layer_import": (c.c_int, [P, c.c_int, c.c_int, i64, P]),
         "dissem_send": (c.c_int, [P, c.c_int, c.c_int, c.c_int, i64, i64, i64, c.POINTER(i64)]),
@@ -147,6 +148,23 @@ def plan_relay(xfers: List["Xfer"], pieces: int = 16) -> List["Xfer"]:
     return res
 
 
+class HostBuffer:
+    """Pinned, GPU-mapped host memory from dissem_host_alloc, viewable as a numpy array."""
+
+    def __init__(self, size: int):
+        self.size = size
+        self._p = ctypes.c_void_p()
+        _check(lib().dissem_host_alloc(ctypes.byref(self._p), size))
+        self.ptr = self._p.value
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * max(size, 1)).from_address(self.ptr))[:size]
+
+    def free(self):
+        if self._p:
+            self.array = None
+            _check(lib().dissem_host_free(self._p))
+            self._p = ctypes.c_void_p()
+
+
 NOALLOC_MAX_CHUNKS = 8192
 
 
@@ -218,6 +236,10 @@ class Engine:
         out = np.empty(size, dtype=np.uint8)
         _check(lib().dissem_layer_read(self._ctx, node, layer, out.ctypes.data, off, size))
         return out
+
+    def attach_host(self, node: int, layer: int, ptr: int, size: int):
+        """Register pinned, GPU-mapped host memory (dissem_host_alloc) as the node's copy of the layer (source only)."""
+        _check(lib().dissem_layer_attach_host(self._ctx, node, layer, ptr, size))
 
     def export(self, node: int, layer: int) -> bytes:
         buf = (ctypes.c_uint8 * 64)()

@@ -68,6 +68,7 @@ struct DeviceState {
 struct SchedPart {
     int dev_slot = -1;
     int round = 0;
+    bool host_src = false;            // reads pinned host memory: runs the register kernel
     XferDesc *d_descs = nullptr;
     int n_descs = 0;
     long long total_units = 0;
@@ -333,6 +334,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         std::vector<XferDesc> descs;
         long long units = 0;
         int64_t bytes = 0;
+        bool any_host_src = false;
         for (auto &it : by_dev[slot]) {
             const dissem_xfer &x = it.x;
             LayerBuf *src = nullptr, *dst = nullptr;
@@ -358,6 +360,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                     return set_error(DISSEM_ERANGE, "layer %d: total %lld but src holds %lld and dst %lld bytes", x.layer,
                                      (long long)x.total, (long long)src->size, (long long)dst->size);
                 if (src->base == dst->base) return set_error(DISSEM_EINVAL, "layer %d: source and destination are the same buffer", x.layer);
+                if (dst->host) return set_error(DISSEM_ENOTSUP, "layer %d: node %d holds it in attached host memory, which can only be a source", x.layer, x.dst_node);
                 d.dst = dst->base;
                 d.csum = dst->csum();
                 d.received = dst->received();
@@ -366,6 +369,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             units += units_of(x.off, x.size, out->unit_shift);
             bytes += x.size * (int64_t)it.n_dsts;
             descs.push_back(d);
+            if (src->host) any_host_src = true;
         }
         // stripe order (dissem_kernels.cuh): sort by unit count, then store each level's starting ticket
         std::stable_sort(descs.begin(), descs.end(), [&](const XferDesc &a, const XferDesc &b) {
@@ -386,6 +390,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         SchedPart part;
         part.dev_slot = (int)slot;
         part.round = rounds[ri];
+        part.host_src = any_host_src;
         part.n_descs = (int)descs.size();
         part.total_units = units;
         part.bytes = bytes;
@@ -480,7 +485,7 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
             CUDA_TRY(cudaSetDevice(ds.dev));
             for (size_t m = i; m < j; ++m)
                 if (m != k) CUDA_TRY(cudaStreamWaitEvent(ds.stream, t->parts[first_tp + (m - i)].mid, 0));
-            LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
+            LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, p.host_src ? 0 : (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
             CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
             CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
             this_round.push_back(tp.end);
@@ -584,6 +589,7 @@ int dissem_close(dissem_ctx *ctx) {
         for (int n = 0; n < ctx->n_nodes; ++n)
             for (auto &kv : ctx->layers[n]) {
                 LayerBuf &lb = kv.second;
+                if (lb.host) continue;
                 if (lb.imported) cudaIpcCloseMemHandle(lb.base);
                 else if (lb.vmm) vmm_free(&lb.blk);
                 else {
@@ -656,7 +662,8 @@ int dissem_layer_free(dissem_ctx *ctx, int node, int layer) {
             it = ctx->mcasts.erase(it);
         } else ++it;
     }
-    if (lb->imported) CUDA_TRY(cudaIpcCloseMemHandle(lb->base));
+    if (lb->host) { /* caller-owned memory: nothing to release */ }
+    else if (lb->imported) CUDA_TRY(cudaIpcCloseMemHandle(lb->base));
     else if (lb->vmm) vmm_free(&lb->blk);
     else {
         CUDA_TRY(cudaSetDevice(lb->device));
@@ -708,6 +715,7 @@ int dissem_layer_reset(dissem_ctx *ctx, int node, int layer) {
     if (rc) return rc;
     rc = local_dev(ctx, node, &ds);
     if (rc) return rc;
+    if (lb->host) return DISSEM_OK;
     CUDA_TRY(cudaSetDevice(ds->dev));
     CUDA_TRY(cudaMemsetAsync(lb->base + lb->trailer_off(), 0, (size_t)lb->trailer_bytes(), ds->stream));
     return DISSEM_OK;
@@ -754,12 +762,36 @@ int dissem_layer_read(dissem_ctx *ctx, int node, int layer, void *host, int64_t 
 
 int dissem_host_alloc(void **out, int64_t size) {
     if (!out || size < 0) return set_error(DISSEM_EINVAL, "dissem_host_alloc: bad arguments");
-    CUDA_TRY(cudaHostAlloc(out, (size_t)std::max<int64_t>(size, 1), cudaHostAllocPortable));
+    CUDA_TRY(cudaHostAlloc(out, (size_t)std::max<int64_t>(size, 1), cudaHostAllocPortable | cudaHostAllocMapped));
     return DISSEM_OK;
 }
 int dissem_host_free(void *p) {
     if (!p) return DISSEM_OK;
     CUDA_TRY(cudaFreeHost(p));
+    return DISSEM_OK;
+}
+
+int dissem_layer_attach_host(dissem_ctx *ctx, int node, int layer, void *pinned, int64_t size) {
+    if (!ctx || (!pinned && size > 0) || size < 0) return set_error(DISSEM_EINVAL, "dissem_layer_attach_host: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceState *ds = nullptr;
+    int rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    if (ctx->layers[node].count(layer)) return set_error(DISSEM_EEXIST, "node %d already holds layer %d", node, layer);
+    if (reinterpret_cast<uintptr_t>(pinned) % 16) return set_error(DISSEM_EINVAL, "host layers must be 16-byte aligned");
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    void *dptr = nullptr;
+    cudaError_t e = cudaHostGetDevicePointer(&dptr, pinned, 0);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return set_error(DISSEM_EINVAL, "the buffer is not pinned, GPU-mapped host memory (use dissem_host_alloc): %s", cudaGetErrorString(e));
+    }
+    LayerBuf lb;
+    lb.size = size;
+    lb.base = static_cast<uint8_t *>(dptr);
+    lb.device = ds->dev;
+    lb.host = true;
+    ctx->layers[node][layer] = lb;
     return DISSEM_OK;
 }
 
@@ -770,6 +802,7 @@ int dissem_layer_export(dissem_ctx *ctx, int node, int layer, uint8_t handle_out
     int rc = find_layer(ctx, node, layer, &lb);
     if (rc) return rc;
     if (lb->imported) return set_error(DISSEM_EINVAL, "layer %d of node %d is itself imported", layer, node);
+    if (lb->host) return set_error(DISSEM_ENOTSUP, "layer %d of node %d is attached host memory; peers read pinned host memory of their own process only", layer, node);
     if (lb->vmm) return set_error(DISSEM_ENOTSUP, "layer %d of node %d is VMM-backed (alloc_vmm); cross-process export of such layers is not implemented", layer, node);
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     cudaIpcMemHandle_t h;
@@ -1044,6 +1077,7 @@ static int read_trailer(dissem_ctx *ctx, int node, int layer, int64_t byte_off, 
     DeviceState *ds = nullptr;
     int rc = find_layer(ctx, node, layer, &lb);
     if (rc) return rc;
+    if (lb->host) return set_error(DISSEM_ENOTSUP, "an attached host layer has no checksum table or received counter (it is a source)");
     rc = local_dev(ctx, node, &ds);
     if (rc) return rc;
     for (auto &d : ctx->devs) {
@@ -1111,7 +1145,7 @@ int dissem_layer_verify(dissem_ctx *ctx, int node, int layer, uint64_t *out, int
     cudaError_t e = cudaMemsetAsync(scratch, 0, 256 + table_bytes, ds->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(scratch, &d, sizeof d, cudaMemcpyHostToDevice, ds->stream);
     if (e == cudaSuccess) {
-        LaunchCfg cfg{ds->n_sm, (int)ctx->opt_ctas_per_sm, (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
+        LaunchCfg cfg{ds->n_sm, (int)ctx->opt_ctas_per_sm, lb->host ? 0 : (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
         e = launch_copy_csum(reinterpret_cast<XferDesc *>(scratch), 1, units_of(0, lb->size, kChunkShift), kChunkShift,
                              ds->counters, cfg, ds->stream, nullptr);
     }

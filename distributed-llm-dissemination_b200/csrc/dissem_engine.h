@@ -16,6 +16,7 @@ struct LayerBuf {
     uint8_t *base = nullptr;
     int device = -1;        // CUDA ordinal of the owning device; -1 for an imported (remote) layer
     bool imported = false;
+    bool host = false;      // a caller-owned pinned host buffer attached as this node's copy (source only, no trailer)
     bool vmm = false;       // allocated through the VMM API (can be bound to an NVLS multicast object)
     VmmBlock blk;
 

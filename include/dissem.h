@@ -105,8 +105,14 @@ int dissem_layer_reset(dissem_ctx *ctx, int node, int layer);
  * waits for everything submitted so far on the node's device. */
 int dissem_layer_write(dissem_ctx *ctx, int node, int layer, const void *host, int64_t off, int64_t size);
 int dissem_layer_read(dissem_ctx *ctx, int node, int layer, void *host, int64_t off, int64_t size);
-int dissem_host_alloc(void **out, int64_t size); /* pinned host memory for layer bytes */
+int dissem_host_alloc(void **out, int64_t size); /* pinned, GPU-mapped host memory for layer bytes */
 int dissem_host_free(void *p);
+/* The layer stays where the reference keeps it: in host memory (LayerSrc.InmemData, node.go:200-211; the host tier of
+ * SURVEY §8(f).4).  Registers `size` bytes of pinned, GPU-mapped host memory (from dissem_host_alloc; 16-byte aligned;
+ * owned by the caller, who keeps it alive) as `node`'s copy of `layer` WITHOUT copying it: transfers that name it as
+ * their source are read by the copy kernel straight over PCIe, so upload and dissemination are one pass.  Such a
+ * copy can only be a source: it has no checksum table or received counter and cannot be exported. */
+int dissem_layer_attach_host(dissem_ctx *ctx, int node, int layer, void *pinned, int64_t size);
 
 /* ---- one process per GPU: make a local layer reachable from peer processes -------------------------- */
 /* handle_out: 64 opaque bytes to ship over the control plane (e.g. inside the announceMsg, message.go:31-41). */

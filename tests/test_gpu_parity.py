@@ -571,3 +571,30 @@ def test_cli_keeps_the_reference_surface():
         assert '"verified":true' in r.stdout and '"ready_equals_assignment":true' in r.stdout
     bad = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", "9"], capture_output=True, text=True, timeout=60)
     assert bad.returncode != 0 and "unknown mode" in bad.stderr
+
+
+def test_host_resident_source_layers():
+    """a layer that stays in (pinned) host memory is a transfer source; the kernel reads it over PCIe."""
+    size = 5 * d.CHUNK_BYTES + 1234 + 2          # not a multiple of 4 either
+    want = o.fill_bytes(o.FILL_PATTERN, 6, size, SEED)
+    hb = d.HostBuffer(size)
+    try:
+        hb.array[:] = want
+        with d.Engine([0, 0, 0]) as eng:
+            eng.attach_host(0, 6, hb.ptr, size)
+            for dst in (1, 2):
+                eng.alloc(dst, 6, size)
+                eng.fill(dst, 6, d.FILL_POISON)
+            assert np.array_equal(eng.verify(0, 6), o.checksum(want))             # read-only pass over host memory
+            eng.wait(eng.submit([(0, 1, 6, 0, size, size), (0, 2, 6, 0, 100_003, size), (0, 2, 6, 100_003, size - 100_003, size)]))
+            for dst in (1, 2):
+                assert np.array_equal(eng.read(dst, 6), want)
+                assert np.array_equal(eng.checksums(dst, 6), o.checksum(want))
+                assert eng.received(dst, 6) == size
+            with pytest.raises(d.DissemError) as e:
+                eng.send(1, 0, 6, 0, size, size)                                   # a host copy cannot be a destination
+            assert e.value.code == -8
+            with pytest.raises(d.DissemError):
+                eng.checksums(0, 6)
+    finally:
+        hb.free()
