@@ -1166,7 +1166,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     else if (k == "alloc_vmm") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0 or 1"); ctx->opt_alloc_vmm = value; }
     else if (k == "mcast") { if (value < 0 || value > 3) return set_error(DISSEM_EINVAL, "mcast must be 0..3"); ctx->opt_mcast = value; }
     else if (k == "pull") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "pull must be 0, 1 or 2"); ctx->opt_pull = value; }
-    else if (k == "reg_cfg") { if (value < 0 || value > 6) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..6"); ctx->opt_reg_cfg = value; }
+    else if (k == "reg_cfg") { if (value < 0 || value > 9) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..9"); ctx->opt_reg_cfg = value; }
     else if (k == "unit_bytes") {
         if (value != 0 && (value < 4096 || value > DISSEM_CHUNK_BYTES || (value & (value - 1)))) return set_error(DISSEM_EINVAL, "unit_bytes must be 0 or a power of two in [4096, 262144]");
         ctx->opt_unit_bytes = value;

@@ -31,6 +31,20 @@ __device__ __forceinline__ void st_stream(uint4 *p, const uint4 &v) {
                  "r"(v.z), "r"(v.w)
                  : "memory");
 }
+// 256-bit forms (sm_100+): a warp then moves 1 KiB of contiguous bytes per instruction.
+struct U8 { uint4 lo, hi; };
+__device__ __forceinline__ U8 ld_stream32(const void *p) {
+    U8 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream32(void *p, const U8 &v) {
+    asm volatile("st.global.L1::no_allocate.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v.lo.x), "r"(v.lo.y),
+                 "r"(v.lo.z), "r"(v.lo.w), "r"(v.hi.x), "r"(v.hi.y), "r"(v.hi.z), "r"(v.hi.w)
+                 : "memory");
+}
 // NVLS: one store lands in every GPU bound to the multicast object.
 __device__ __forceinline__ void st_multicast(uint4 *p, const uint4 &v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p),
@@ -70,7 +84,7 @@ struct Acc {
 // ------------------------------------------------------------------------------------------------
 // K1/K4/K5 (register path): copy + checksum, checksum only when dst == NULL.
 // ------------------------------------------------------------------------------------------------
-template <int kThreads, int kUnroll>
+template <int kThreads, int kUnroll, bool kWide = false>
 __global__ void __launch_bounds__(kThreads)
 copy_csum_kernel(const XferDesc *__restrict__ descs, int n_descs, long long total_units, int unit_shift,
                  SchedCounters *counters) {
@@ -123,6 +137,38 @@ copy_csum_kernel(const XferDesc *__restrict__ descs, int n_descs, long long tota
         const unsigned int k_body = (unsigned int)((a0 >> 2) - base_word);
 
         long long v = tid;
+        if constexpr (kWide) {
+            // 32-byte vectors when the body starts 32-byte aligned (every whole unit does) and is not a multicast unit
+            if (((a0 & 31) == 0) && !mc) {
+                const long long n32 = (a1 - a0) >> 5;
+                const uint8_t *sb = src + a0;
+                uint8_t *db = dst ? dst + a0 : nullptr;
+                long long w = tid;
+                for (; w + (long long)(kUnroll - 1) * kThreads < n32; w += (long long)kUnroll * kThreads) {
+                    U8 r[kUnroll];
+#pragma unroll
+                    for (int j = 0; j < kUnroll; ++j) r[j] = ld_stream32(sb + ((w + j * kThreads) << 5));
+                    if (db) {
+#pragma unroll
+                        for (int j = 0; j < kUnroll; ++j) st_stream32(db + ((w + j * kThreads) << 5), r[j]);
+                    }
+#pragma unroll
+                    for (int j = 0; j < kUnroll; ++j) {
+                        const unsigned int k0 = k_body + 8u * (unsigned int)(w + j * kThreads);
+                        acc.vec(r[j].lo, k0);
+                        acc.vec(r[j].hi, k0 + 4u);
+                    }
+                }
+                for (; w < n32; w += kThreads) {
+                    const U8 r = ld_stream32(sb + (w << 5));
+                    if (db) st_stream32(db + (w << 5), r);
+                    const unsigned int k0 = k_body + 8u * (unsigned int)w;
+                    acc.vec(r.lo, k0);
+                    acc.vec(r.hi, k0 + 4u);
+                }
+                v = 2 * n32 + tid;                       // at most one 16-byte vector is left for the loop below
+            }
+        }
         // full tiles: kUnroll independent 16-byte loads in flight per thread, then the stores
         for (; v + (long long)(kUnroll - 1) * kThreads < nvec; v += (long long)kUnroll * kThreads) {
             uint4 r[kUnroll];
@@ -266,14 +312,14 @@ cudaError_t launch_zero_csum(const XferDesc *descs, int n_descs, cudaStream_t st
     return cudaGetLastError();
 }
 
-template <int kThreads, int kUnroll>
+template <int kThreads, int kUnroll, bool kWide = false>
 static cudaError_t launch_reg(const XferDesc *descs, int n_descs, long long total_units, int unit_shift,
                               SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream,
                               int *grid_out) {
     int per_sm = cfg.ctas_per_sm;
     if (per_sm <= 0) {
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-            &per_sm, copy_csum_kernel<kThreads, kUnroll>, kThreads, 0);
+            &per_sm, copy_csum_kernel<kThreads, kUnroll, kWide>, kThreads, 0);
         if (e != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
     }
@@ -281,7 +327,7 @@ static cudaError_t launch_reg(const XferDesc *descs, int n_descs, long long tota
     if (grid > total_units) grid = total_units;
     if (grid < 1) grid = 1;
     if (grid_out) *grid_out = (int)grid;
-    copy_csum_kernel<kThreads, kUnroll><<<(int)grid, kThreads, 0, stream>>>(descs, n_descs, total_units,
+    copy_csum_kernel<kThreads, kUnroll, kWide><<<(int)grid, kThreads, 0, stream>>>(descs, n_descs, total_units,
                                                                             unit_shift, counters);
     return cudaGetLastError();
 }
@@ -303,6 +349,9 @@ cudaError_t launch_copy_csum(const XferDesc *descs, int n_descs, long long total
         case 4: return launch_reg<1024, 4>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
         case 5: return launch_reg<1024, 2>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
         case 6: return launch_reg<512, 2>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 7: return launch_reg<512, 2, true>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 8: return launch_reg<512, 4, true>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 9: return launch_reg<256, 4, true>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
         default: return launch_reg<512, 4>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
     }
 }

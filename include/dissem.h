@@ -200,7 +200,7 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
 /* ---- tuning / introspection -------------------------------------------------------------------------- */
 /* key: "ctas_per_sm" (0 = occupancy-derived), "variant" (0 = register path, 1 = TMA bulk-staged path),
  * "reg_cfg" (register-path shape, threads x 16-byte loads in flight: 0 256x4, 1 512x4 (default), 2 256x8,
- * 3 512x8, 4 1024x4, 5 1024x2, 6 512x2),
+ * 3 512x8, 4 1024x4, 5 1024x2, 6 512x2; 7/8/9 = 512x2, 512x4, 256x4 with 32-byte loads and stores),
  * "tma_cfg" (TMA ring shape, stage bytes x stages: 0 16Kx6 (default), 1 32Kx3, 2 8Kx12, 3 16Kx4, 4 8Kx6, 5 4Kx12),
  * "alloc_vmm" (1 = dissem_layer_alloc uses the VMM API so that layers can be bound to NVLS multicast objects;
  *  such layers cannot be exported to other processes yet),

@@ -166,10 +166,11 @@ def test_plan_schedule_matches_oracle_store(mode, policy, unit_bytes):
             assert eng.received(x.dst_node, x.layer) == x.total
 
 
-@pytest.mark.parametrize("reg_cfg", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("reg_cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9])
 def test_kernel_shapes_agree(reg_cfg):
     size = 5 * d.CHUNK_BYTES + 123
     with d.Engine([0, 0]) as eng:
+        eng.set_option("variant", 0)
         eng.set_option("reg_cfg", reg_cfg)
         eng.alloc(0, 0, size)
         eng.fill(0, 0, d.FILL_PATTERN, 9)

@@ -10,6 +10,9 @@ SIZE, NL = 256 << 20, 4
 pull = len(sys.argv) > 1 and sys.argv[1] == "pull"
 with d.Engine([0, 1]) as eng:
     eng.set_option("pull", 1 if pull else 0)
+    if len(sys.argv) > 2:
+        eng.set_option("variant", 0)
+        eng.set_option("reg_cfg", int(sys.argv[2]))
     for l in range(NL):
         eng.alloc(0, l, SIZE)
         eng.fill(0, l, d.FILL_PATTERN, 1)
@@ -17,5 +20,5 @@ with d.Engine([0, 1]) as eng:
     s = eng.compile([(0, 1, l, 0, SIZE, SIZE) for l in range(NL)])
     ts = [eng.wait_detail(eng.launch(s))[1] for _ in range(4)]
     ok = bool((eng.checksums(1, 0) == eng.verify(0, 0)).all())
-    print(json.dumps({"mode": "pull" if pull else "push", "bytes_per_launch": NL * SIZE, "kernel_ms": ts,
+    print(json.dumps({"mode": "pull" if pull else "push", "reg_cfg": (int(sys.argv[2]) if len(sys.argv) > 2 else "tma"), "bytes_per_launch": NL * SIZE, "kernel_ms": ts,
                       "GBps_best": NL * SIZE / min(ts) / 1e6, "verified": ok}))
