@@ -77,3 +77,34 @@ def link_bytes(xfers: Iterable, owner: Callable[[int], int], world: int):
             egress[s] += x.size
             ingress[d] += x.size
     return egress, ingress, local
+
+
+def split_rounds(xfers: Sequence) -> List[List]:
+    """Transfers grouped by their round (DISSEM_XFER_ROUND bits), ascending."""
+    by: Dict[int, List] = {}
+    for x in xfers:
+        by.setdefault((getattr(x, "flags", 0) >> 8) & 0xFFFF, []).append(x)
+    return [by[r] for r in sorted(by)]
+
+
+class RoundedSchedule:
+    """A plan with rounds (e.g. from dissem_plan_relay) in the one-process-per-GPU model.  Inside one process the engine
+    orders rounds on the device; ACROSS processes nothing does, so each round is compiled as its own schedule and the
+    ranks meet at `barrier()` (a torch.distributed barrier + device synchronise) between rounds."""
+
+    def __init__(self, eng, xfers: Sequence):
+        self.eng = eng
+        self.scheds = [eng.compile(r) for r in split_rounds(xfers)]
+
+    def run(self, barrier: Callable[[], None]) -> float:
+        """Launch every round in turn; returns this rank's summed device milliseconds."""
+        ms = 0.0
+        for s in self.scheds:
+            ms += self.eng.wait(self.eng.launch(s))
+            barrier()
+        return ms
+
+    def free(self):
+        for s in self.scheds:
+            self.eng.sched_free(s)
+        self.scheds = []
