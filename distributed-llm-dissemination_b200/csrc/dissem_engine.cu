@@ -63,10 +63,17 @@ struct DeviceState {
     int n_sm = 0;
     cudaStream_t stream = nullptr;
     SchedCounters *counters = nullptr;   // kernel scratch: ticket + drained-CTA count
+    // Descriptor tables of small schedules (one Transport.Send = one descriptor) come from this pool instead of a
+    // cudaMalloc/cudaFree pair per message (cudaFree waits for the whole device).
+    XferDesc *desc_pool = nullptr;
+    std::vector<int> free_slots;
 };
+constexpr int kPoolSlots = 256;
+constexpr int kSlotDescs = 16;
 
 struct SchedPart {
     int dev_slot = -1;
+    int pool_slot = -1;               // >= 0: d_descs points into the device's descriptor pool
     int round = 0;
     bool host_src = false;            // reads pinned host memory: runs the register kernel
     XferDesc *d_descs = nullptr;
@@ -106,6 +113,7 @@ struct dissem_ctx {
     std::map<std::pair<int, std::vector<int>>, McObject> mcasts;
     int64_t mcast_groups_compiled = 0;
     std::string mcast_note;
+    std::vector<cudaEvent_t> event_pool[64];   // per device ordinal: events are reused across launches
     // options
     int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0, opt_alloc_vmm = 0, opt_mcast = 1;
 };
@@ -138,7 +146,8 @@ static int local_dev(dissem_ctx *ctx, int node, DeviceState **out) {
 
 static void free_sched(dissem_ctx *ctx, Sched &s) {
     for (auto &p : s.parts) {
-        if (p.d_descs) {
+        if (p.pool_slot >= 0) ctx->devs[p.dev_slot].free_slots.push_back(p.pool_slot);
+        else if (p.d_descs) {
             cudaSetDevice(ctx->devs[p.dev_slot].dev);
             cudaFree(p.d_descs);
         }
@@ -443,13 +452,31 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
     }
     for (size_t pi = 0; pi < out->parts.size(); ++pi) {
         SchedPart &part = out->parts[pi];
-        CUDA_TRY(cudaSetDevice(ctx->devs[part.dev_slot].dev));
-        CUDA_TRY(cudaMalloc(&part.d_descs, part_descs[pi].size() * sizeof(XferDesc)));
+        DeviceState &pds = ctx->devs[part.dev_slot];
+        CUDA_TRY(cudaSetDevice(pds.dev));
+        if ((int)part_descs[pi].size() <= kSlotDescs && !pds.free_slots.empty()) {
+            // a slot is reused only by work enqueued later on the same stream, so the previous user has finished with it
+            part.pool_slot = pds.free_slots.back();
+            pds.free_slots.pop_back();
+            part.d_descs = pds.desc_pool + (size_t)part.pool_slot * kSlotDescs;
+        } else {
+            CUDA_TRY(cudaMalloc(&part.d_descs, part_descs[pi].size() * sizeof(XferDesc)));
+        }
         // stream-ordered upload from pageable memory: the copy is staged before the call returns
         CUDA_TRY(cudaMemcpyAsync(part.d_descs, part_descs[pi].data(), part_descs[pi].size() * sizeof(XferDesc),
                                  cudaMemcpyHostToDevice, ctx->devs[part.dev_slot].stream));
     }
     return 0;
+}
+
+static cudaError_t take_event(dissem_ctx *ctx, int dev, cudaEvent_t *out) {
+    auto &pool = ctx->event_pool[dev & 63];
+    if (!pool.empty()) {
+        *out = pool.back();
+        pool.pop_back();
+        return cudaSuccess;
+    }
+    return cudaEventCreate(out);
 }
 
 static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
@@ -469,10 +496,13 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
             for (cudaEvent_t ev : prev_round) CUDA_TRY(cudaStreamWaitEvent(ds.stream, ev, 0));
             TicketPart tp;
             tp.dev_slot = p.dev_slot;
-            CUDA_TRY(cudaEventCreate(&tp.start));
-            CUDA_TRY(cudaEventCreate(&tp.mid));
-            CUDA_TRY(cudaEventCreate(&tp.end));
+            tp.start = tp.mid = tp.end = nullptr;
             t->parts.push_back(tp);
+            TicketPart &ntp = t->parts.back();
+            CUDA_TRY(take_event(ctx, ds.dev, &ntp.start));
+            CUDA_TRY(take_event(ctx, ds.dev, &ntp.mid));
+            CUDA_TRY(take_event(ctx, ds.dev, &ntp.end));
+            tp = ntp;
             CUDA_TRY(cudaEventRecord(tp.start, ds.stream));
             CUDA_TRY(launch_zero_csum(p.d_descs, p.n_descs, ds.stream));
             CUDA_TRY(cudaEventRecord(tp.mid, ds.stream));
@@ -496,11 +526,12 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
     return 0;
 }
 
-static void drop_ticket(Ticket &t) {
+// caller holds ctx->mu
+static void drop_ticket(dissem_ctx *ctx, Ticket &t) {
     for (auto &p : t.parts) {
-        cudaEventDestroy(p.start);
-        cudaEventDestroy(p.mid);
-        cudaEventDestroy(p.end);
+        auto &pool = ctx->event_pool[ctx->devs[p.dev_slot].dev & 63];
+        for (cudaEvent_t ev : {p.start, p.mid, p.end})
+            if (ev) pool.push_back(ev);
     }
     t.parts.clear();
 }
@@ -552,6 +583,8 @@ int dissem_init(int n_nodes, const int *device_of_node, dissem_ctx **out) {
             CUDA_TRY(cudaStreamCreateWithFlags(&ds.stream, cudaStreamNonBlocking));
             CUDA_TRY(cudaMalloc(&ds.counters, sizeof(SchedCounters)));
             CUDA_TRY(cudaMemset(ds.counters, 0, sizeof(SchedCounters)));
+            CUDA_TRY(cudaMalloc(&ds.desc_pool, (size_t)kPoolSlots * kSlotDescs * sizeof(XferDesc)));
+            for (int sl = kPoolSlots - 1; sl >= 0; --sl) ds.free_slots.push_back(sl);
             CUDA_TRY(warm_kernels());
             ctx->devs.push_back(ds);
             slot = (int)ctx->devs.size() - 1;
@@ -582,7 +615,11 @@ int dissem_close(dissem_ctx *ctx) {
             cudaSetDevice(ds.dev);
             cudaStreamSynchronize(ds.stream);
         }
-        for (auto &kv : ctx->tickets) drop_ticket(kv.second);
+        for (auto &kv : ctx->tickets) drop_ticket(ctx, kv.second);
+        for (auto &pool : ctx->event_pool) {
+            for (cudaEvent_t ev : pool) cudaEventDestroy(ev);
+            pool.clear();
+        }
         for (auto &kv : ctx->scheds) free_sched(ctx, kv.second);
         for (auto &kv : ctx->mcasts) mcast_destroy(&kv.second);
         ctx->mcasts.clear();
@@ -600,6 +637,7 @@ int dissem_close(dissem_ctx *ctx) {
         for (auto &ds : ctx->devs) {
             cudaSetDevice(ds.dev);
             cudaFree(ds.counters);
+            cudaFree(ds.desc_pool);
             cudaStreamDestroy(ds.stream);
         }
     }
@@ -859,7 +897,7 @@ int dissem_schedule_launch(dissem_ctx *ctx, dissem_sched sched, dissem_ticket *o
     Ticket t;
     int rc = launch_sched(ctx, it->second, &t);
     if (rc) {
-        drop_ticket(t);
+        drop_ticket(ctx, t);
         return rc;
     }
     int64_t id = ctx->next_id++;
@@ -1043,9 +1081,9 @@ int dissem_wait_detail(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out, do
             ms = std::max(ms, (double)f);
             copy_ms = std::max(copy_ms, copy_sum[kv.first]);
         }
-    drop_ticket(t);
     {
         std::lock_guard<std::mutex> lk(ctx->mu);
+        drop_ticket(ctx, t);
         auto sit = ctx->scheds.find(-ticket);       // schedule parked by dissem_schedule_submit
         if (sit != ctx->scheds.end()) {
             free_sched(ctx, sit->second);
