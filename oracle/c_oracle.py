@@ -64,8 +64,16 @@ def tcp_run(n_nodes: int, leader: int, xfers: Sequence, src_layers: Sequence[np.
         ptrs[i] = src_layers[i].ctypes.data
     sec = ctypes.c_double(0.0)
     moved = ctypes.c_int64(0)
-    rc = lib().oracle_tcp_run(n_nodes, leader, base_port, arr, n, ptrs, int(verify),
-                              ctypes.byref(sec), ctypes.byref(moved))
+    # a port of the block may be taken on a shared box: try a few blocks before giving up
+    rc = -1
+    for attempt in range(6):
+        port = base_port + attempt * 997
+        if port + n_nodes >= 65000:
+            port = 20000 + (port % 20000)
+        rc = lib().oracle_tcp_run(n_nodes, leader, port, arr, n, ptrs, int(verify),
+                                  ctypes.byref(sec), ctypes.byref(moved))
+        if rc == 0 or rc == -2:
+            break
     if rc != 0:
-        raise RuntimeError(f"oracle_tcp_run failed rc={rc}")
+        raise RuntimeError(f"oracle_tcp_run failed rc={rc}" + (" (delivered bytes differ from the source)" if rc == -2 else ""))
     return sec.value, moved.value
