@@ -75,6 +75,9 @@ def load_library() -> ctypes.CDLL:
         "dissem_schedule_info": (c.c_int, [P, i64, c.POINTER(i64), c.POINTER(c.c_int), c.POINTER(i64)]),
         "dissem_plan_directions": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int]),
         "dissem_plan_relay": (c.c_int, [c.POINTER(Xfer), c.c_int, c.c_int, c.POINTER(c.POINTER(Xfer)), c.POINTER(c.c_int)]),
+        "dissem_plan_optimize": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.POINTER(Xfer)),
+                                           c.POINTER(c.c_int), c.POINTER(c.c_int)]),
+        "dissem_node_device": (c.c_int, [P, c.c_int, c.POINTER(c.c_int)]),
         "dissem_wait": (c.c_int, [P, i64, c.POINTER(c.c_double)]),
         "dissem_wait_detail": (c.c_int, [P, i64, c.POINTER(c.c_double), c.POINTER(c.c_double)]),
         "dissem_poll": (c.c_int, [P, i64, c.POINTER(c.c_int)]),
@@ -146,6 +149,23 @@ def plan_relay(xfers: List["Xfer"], pieces: int = 16) -> List["Xfer"]:
     L.dissem_free.argtypes = [ctypes.c_void_p]
     L.dissem_free(ctypes.cast(out, ctypes.c_void_p))
     return res
+
+
+def plan_optimize(xfers: List["Xfer"], gpu_of_node: Sequence[int]):
+    """dissem_plan_optimize: relay chains when they unload the busiest port, then push/pull per transfer.
+    Returns (transfers, relay_pieces) with relay_pieces == 0 when the plan was left as unicast."""
+    arr = make_xfers(xfers)
+    g = (ctypes.c_int * len(gpu_of_node))(*gpu_of_node)
+    out = ctypes.POINTER(Xfer)()
+    n_out, pieces = ctypes.c_int(), ctypes.c_int()
+    L = lib()
+    _check(L.dissem_plan_optimize(arr, len(xfers), g, len(gpu_of_node), ctypes.byref(out), ctypes.byref(n_out), ctypes.byref(pieces)))
+    res = [Xfer(out[i].src_node, out[i].dst_node, out[i].layer, out[i].flags, out[i].off, out[i].size, out[i].total)
+           for i in range(n_out.value)]
+    L.dissem_free.restype = None
+    L.dissem_free.argtypes = [ctypes.c_void_p]
+    L.dissem_free(ctypes.cast(out, ctypes.c_void_p))
+    return res, pieces.value
 
 
 class HostBuffer:

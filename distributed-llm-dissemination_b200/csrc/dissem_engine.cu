@@ -1041,6 +1041,81 @@ int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **ou
     return DISSEM_OK;
 }
 
+int dissem_plan_optimize(const dissem_xfer *in, int n, const int *gpu_of_node, int n_nodes, dissem_xfer **out, int *n_out,
+                         int *relay_pieces_out) {
+    if (n < 0 || (n > 0 && !in) || !gpu_of_node || n_nodes <= 0 || !out || !n_out)
+        return set_error(DISSEM_EINVAL, "dissem_plan_optimize: bad arguments");
+    for (int i = 0; i < n; ++i)
+        if (in[i].src_node < 0 || in[i].src_node >= n_nodes || in[i].dst_node < 0 || in[i].dst_node >= n_nodes)
+            return set_error(DISSEM_ENOENT, "transfer %d names a node outside [0,%d)", i, n_nodes);
+    // busiest-port bytes of a transfer list (transfers inside one GPU do not use a port)
+    auto busiest = [&](const dissem_xfer *xs, int cnt) {
+        std::map<int, int64_t> eg, ing;
+        for (int i = 0; i < cnt; ++i) {
+            const int gs = gpu_of_node[xs[i].src_node], gd = gpu_of_node[xs[i].dst_node];
+            if (gs == gd) continue;
+            eg[gs] += xs[i].size;
+            ing[gd] += xs[i].size;
+        }
+        int64_t m = 0;
+        for (auto &kv : eg) m = std::max(m, kv.second);
+        for (auto &kv : ing) m = std::max(m, kv.second);
+        return m;
+    };
+    // are there transfers of the same bytes from one source to several GPUs at all?
+    bool fanout = false;
+    int64_t biggest = 0;
+    for (int i = 0; i < n && !fanout; ++i)
+        for (int j = i + 1; j < n; ++j)
+            if (in[j].src_node == in[i].src_node && in[j].layer == in[i].layer && in[j].off == in[i].off &&
+                in[j].size == in[i].size && gpu_of_node[in[j].dst_node] != gpu_of_node[in[i].dst_node]) { fanout = true; break; }
+    for (int i = 0; i < n; ++i) biggest = std::max(biggest, in[i].size);
+    dissem_xfer *chosen = nullptr;
+    int n_chosen = 0, pieces_used = 0;
+    if (fanout && biggest >= (8ll << 20)) {
+        // relay chains: the source sends once, destinations forward; costs (pieces + hops - 1) / pieces in pipeline fill.
+        // Pieces of ~64 MiB keep a round long enough to hide its launch and barrier costs (profiles/r01_summary.md).
+        int pieces = (int)std::min<int64_t>(32, std::max<int64_t>(4, biggest / (64ll << 20)));
+        dissem_xfer *relay = nullptr;
+        int n_relay = 0;
+        int rc = dissem_plan_relay(in, n, pieces, &relay, &n_relay);
+        if (rc) return rc;
+        int max_round = 0;
+        for (int i = 0; i < n_relay; ++i) max_round = std::max(max_round, (relay[i].flags >> DISSEM_XFER_ROUND_SHIFT) & 0xFFFF);
+        const double t_uni = (double)busiest(in, n);
+        const double t_relay = (double)busiest(relay, n_relay) * (double)(max_round + 1) / (double)pieces;
+        if (t_relay < 0.9 * t_uni) {
+            chosen = relay;
+            n_chosen = n_relay;
+            pieces_used = pieces;
+        } else {
+            free(relay);
+        }
+    }
+    if (!chosen) {
+        chosen = (dissem_xfer *)malloc(std::max<size_t>((size_t)n, 1) * sizeof(dissem_xfer));
+        if (!chosen) return set_error(DISSEM_ENOMEM, "out of memory");
+        memcpy(chosen, in, (size_t)n * sizeof(dissem_xfer));
+        n_chosen = n;
+    }
+    int rc = dissem_plan_directions(chosen, n_chosen, gpu_of_node, n_nodes);
+    if (rc) { free(chosen); return rc; }
+    *out = chosen;
+    *n_out = n_chosen;
+    if (relay_pieces_out) *relay_pieces_out = pieces_used;
+    return DISSEM_OK;
+}
+
+int dissem_node_device(dissem_ctx *ctx, int node, int *device_out) {
+    if (!ctx || !device_out) return set_error(DISSEM_EINVAL, "dissem_node_device: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = check_node(ctx, node);
+    if (rc) return rc;
+    const int slot = ctx->node_dev_slot[node];
+    *device_out = slot < 0 ? -1 : ctx->devs[slot].dev;
+    return DISSEM_OK;
+}
+
 int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out) { return dissem_wait_detail(ctx, ticket, ms_out, nullptr); }
 
 int dissem_wait_detail(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out, double *copy_ms_out) {

@@ -1,5 +1,8 @@
 #include "transport.h"
 
+#include <algorithm>
+#include <cstdlib>
+
 #include "../csrc/dissem_engine.h"
 
 namespace dissem {
@@ -133,8 +136,21 @@ int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *de
         d.total = x.TotalSize;
         xs.push_back(d);
     }
+    // let the engine choose relay chains and push/pull directions for this placement of nodes on GPUs
+    const int n_nodes = dissem_n_nodes(fabric_->ctx());
+    std::vector<int> gpu_of_node((size_t)std::max(n_nodes, 0), 0);
+    for (int i = 0; i < n_nodes; ++i) {
+        int rcd = dissem_node_device(fabric_->ctx(), i, &gpu_of_node[i]);
+        if (rcd) return rcd;
+        if (gpu_of_node[i] < 0) gpu_of_node[i] = 1000 + i;            // a node of another process: its own GPU
+    }
+    dissem_xfer *opt = nullptr;
+    int n_opt = 0;
+    int rc = dissem_plan_optimize(xs.data(), (int)xs.size(), gpu_of_node.data(), n_nodes, &opt, &n_opt, nullptr);
+    if (rc) return rc;
     dissem_ticket ticket = 0;
-    int rc = dissem_schedule_submit(fabric_->ctx(), xs.data(), (int)xs.size(), &ticket);
+    rc = dissem_schedule_submit(fabric_->ctx(), opt, n_opt, &ticket);
+    free(opt);
     if (rc) return rc;
     double ms = 0.0;
     rc = dissem_wait(fabric_->ctx(), ticket, &ms);

@@ -157,6 +157,16 @@ int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, in
  * *out is malloc'ed: release it with dissem_free (include/dissem_host.h).  Pure host logic. */
 int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **out, int *n_out);
 
+/* The scheduling decisions above in one call, for a leader that just wants the fastest execution of its plan:
+ * relay chains when the plan has fan-out and the busiest NVLink port gets at least 10 % less to carry that way
+ * (pieces of about 64 MiB; the port load is scaled by the pipeline-fill factor (rounds / pieces)), then
+ * dissem_plan_directions on whatever was chosen.  *relay_pieces_out (may be NULL): pieces used, 0 = no relay.
+ * *out is malloc'ed (dissem_free).  Pure host logic. */
+int dissem_plan_optimize(const dissem_xfer *in, int n, const int *gpu_of_node, int n_nodes, dissem_xfer **out, int *n_out,
+                         int *relay_pieces_out);
+/* CUDA ordinal of the device a local node lives on; -1 for a node of another process. */
+int dissem_node_device(dissem_ctx *ctx, int node, int *device_out);
+
 /* Block until the batch is complete (all bytes visible at their destinations).  ms_out (may be NULL):
  * device time of the batch, max over the source GPUs involved.  The ticket is consumed. */
 int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out);

@@ -259,3 +259,25 @@ def test_mode3_multi_destination_extension():
     text1 = o.config_stage_ring(8, 32, o.S2)
     assert _rows(d.plan(text1, 3, time_scale=1_000_000, flags=host.PLAN_MULTI_DEST)) == _rows(d.plan(text1, 3, time_scale=1_000_000))
     assert _rows(d.plan(o.config_conf_json(), 3, flags=host.PLAN_MULTI_DEST)) == _rows(d.plan(o.config_conf_json(), 3))
+
+
+def test_plan_optimize_picks_relay_only_when_it_unloads_the_busiest_port():
+    size = 1_711_308_800
+
+    def fanout(one_seed, n=8, layers=80):
+        xs = []
+        for l in range(layers):
+            seed = 0 if one_seed else (l + 4) % n
+            dsts = {l % n, (l + 1) % n} | ({(l + 2) % n} if l % 3 >= 1 else set()) | ({(l + 3) % n} if l % 3 == 2 else set())
+            xs += [d.Xfer(seed, dst, l, 0, 0, size, size) for dst in sorted(dsts - {seed})]
+        return xs
+
+    seed_plan, pieces = d.plan_optimize(fanout(True), list(range(8)))
+    assert pieces == 25 and max(d.xfer_round(x) for x in seed_plan) > 0
+    assert sum(x.size for x in seed_plan if x.src_node == 0) == 80 * size          # the seed sends every layer once
+    assert all(x.flags & d.XFER_PULL for x in seed_plan if x.src_node == 0)        # and its hops are pulled
+    bal_plan, pieces = d.plan_optimize(fanout(False), list(range(8)))
+    assert pieces == 0 and len(bal_plan) == 239 and all(d.xfer_round(x) == 0 for x in bal_plan)
+    # everything on one GPU: nothing to optimise
+    one, pieces = d.plan_optimize(fanout(True), [0] * 8)
+    assert pieces == 0 and all(x.flags == 0 for x in one)

@@ -49,7 +49,7 @@ def t_star(xfers, n, multicast):
     return max(max(e, i) for e, i in zip(eg, ing)) / (LINK_GBPS * 1e9), eg, ing
 
 
-def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, variant=1, relay=0):
+def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, variant=1, relay=0, optimize=False):
     eng = d.Engine(list(range(n)))
     try:
         eng.set_option("variant", variant)
@@ -64,6 +64,9 @@ def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, varian
                 eng.fill(x.dst_node, x.layer, d.FILL_POISON)
         xs = d.plan_relay(xfers, relay) if relay else xfers
         xs = d.plan_directions(xs, list(range(n))) if directions else xs
+        if optimize:
+            xs, relay = d.plan_optimize(xfers, list(range(n)))
+            name += f" -> {'relay, %d pieces' % relay if relay else 'unicast'}"
         s = eng.compile(xs)
         groups = eng.get_option("mcast_groups")
         for _ in range(2):
@@ -118,6 +121,9 @@ def main():
             pieces = int("".join(ch for ch in c if ch.isdigit()) or 16)
             run_case(f"{tag}/relay chains, {pieces} pieces" + (" + direction choice" if c.endswith("p") else ""), n, holders,
                      xfers, args.size, vmm=False, mcast=0, directions=c.endswith("p"), reps=args.reps, relay=pieces)
+    if "optimized" in cases:
+        run_case(f"{tag}/dissem_plan_optimize", n, holders, xfers, args.size, vmm=False, mcast=0, directions=False,
+                 reps=args.reps, optimize=True)
     if "mcast_auto" in cases:
         run_case(f"{tag}/NVLS multicast + auto direction for the rest", n, holders, xfers, args.size, vmm=True, mcast=1,
                  directions=True, reps=args.reps)
