@@ -31,3 +31,7 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+# plan_digests.json is produced from the C++ planners (the product), not from the oracle: it pins the plans of every
+# BASELINE configuration x mode so that a later change to host/plan.cpp or host/flow.cpp that alters a plan is noticed.
+# Regenerate with the snippet in tests/test_host_cpu.py::test_plan_digests_are_stable (set REGENERATE = True there).

@@ -1,0 +1,49 @@
+"""bench.py prints ONE JSON line with the keys the driver reads.  The reference arm runs on the CPU (here too); our arm
+needs a GPU."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BASE_KEYS = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+             "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "cpu_baseline"}
+
+
+def _run(*args, timeout=600):
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *args], capture_output=True, text=True,
+                         timeout=timeout, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1, out.stdout[-2000:]
+    return json.loads(lines[0])
+
+
+def test_reference_arm_line():
+    j = _run("--impl", "reference", "--steps", "1", "--warmup", "0")
+    assert BASE_KEYS <= set(j) and j["impl"] == "reference"
+    assert j["metric"] == "dissemination_aggregate_throughput" and j["unit"] == "GB/s" and j["higher_is_better"] is True
+    assert j["value"] > 0 and j["dtype"] == "u8" and j["vs_baseline"] is None and "workload" in j["config"]
+    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["value"] == j["value"]
+    assert j["e2e"] == {"value": j["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert j["gpu_launches"] == 0
+
+
+@pytest.mark.gpu
+def test_our_arm_line():
+    j = _run("--steps", "5", "--warmup", "3")
+    assert BASE_KEYS | {"roofline", "clocks", "verified"} <= set(j) and "impl" not in j
+    assert j["n_gpus"] == 1 and j["steps"] == 5 and j["warmup"] >= 3 and j["scaling"] == "strong" and j["verified"] is True
+    assert j["value"] > 100 and abs(j["ms_per_step"] - j["config"]["delivered_bytes_per_step"] / j["value"] / 1e6) < 1e-6
+    r = j["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    assert r["algorithmic_bytes_per_launch"] == 2 * j["config"]["delivered_bytes_per_step"]
+    e = j["e2e"]
+    assert e["h2d_bytes_per_step"] == j["config"]["delivered_bytes_per_step"] and e["d2h_bytes_per_step"] > 0
+    assert 0 < e["value"] < j["value"]                      # the end-to-end number is its own measurement
+    assert j["gpu_launches"] == 2 * 5
+    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1
+    c = j["clocks"]
+    assert not ({"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} & set(c["reasons"]))

@@ -599,3 +599,16 @@ def test_host_resident_source_layers():
                 eng.checksums(0, 6)
     finally:
         hb.free()
+
+
+def test_mode3_multi_destination_through_roles():
+    """The flow leader with the per-(layer, destination) extension on a fan-out placement: every copy is delivered and
+    verified, per message and as one batched (optimised) schedule."""
+    text = o.config_fanout(n_nodes=4, n_layers=8, size=2 * d.CHUNK_BYTES + 4096)
+    flags = host.PLAN_SIZES_FROM_ANNOUNCES | host.PLAN_MULTI_DEST
+    n = max(1, min(_n_gpus(), 4))
+    for batched in (False, True):
+        r = host.run_distribution(text, 3, node_device=[i % n for i in range(4)], batched=batched, seed=SEED,
+                                  time_scale=1_000_000, flags=flags, timeout_ms=20000)
+        assert r["verified"] and r["ready_equals_assignment"]
+        assert r["layers_checked"] == sum(len(v) for v in o.parse_config(text).assignment.values())

@@ -281,3 +281,35 @@ def test_plan_optimize_picks_relay_only_when_it_unloads_the_busiest_port():
     # everything on one GPU: nothing to optimise
     one, pieces = d.plan_optimize(fanout(True), [0] * 8)
     assert pieces == 0 and all(x.flags == 0 for x in one)
+
+
+def test_plan_digests_are_stable():
+    """Every BASELINE configuration x mode: the C++ planners still produce the committed plans (tests/golden/plan_digests.json),
+    and the oracle agrees with each of them where it restates the mode."""
+    import hashlib
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "plan_digests.json")))
+    cases = {
+        "readme": (o.config_readme(), 1), "identity": (o.config_identity_fixture(), 0), "ring": (o.config_ring_fixture(), 0),
+        "config2_ring_8x32x64MiB": (o.config_stage_ring(8, 32, o.S2), 0),
+        "config3_llama8b": (o.config_stage_ring(8, 32, o.S8B, ring=False), 0),
+        "config4_fanout_70b": (o.config_fanout(), 2 | 4),
+        "config5_seed_8x32x64MiB": (o.config_stage_ring(8, 32, o.S2, ring=False), 0),
+        "conf_json": (o.config_conf_json(), 0),
+    }
+    seen = 0
+    for name, (text, flags) in cases.items():
+        for mode in (0, 1, 2, 3):
+            for ts in ((1, 1_000_000) if mode == 3 else (1,)):
+                key = f"{name}/m{mode}" + (f"/ts{ts}" if mode == 3 else "")
+                want = gold[key]
+                try:
+                    p = d.plan(text, mode, seed=0x5EED, policy=0, time_scale=ts, flags=flags)
+                except d.DissemError as e:
+                    assert want == {"error": e.code}, key
+                    continue
+                rows = [x[:6] for x in p["xfers"]]
+                got = {"n": len(rows), "bytes": sum(r[4] for r in rows), "t": p["t"],
+                       "sha256": hashlib.sha256(json.dumps(rows).encode()).hexdigest()}
+                assert got == want, key
+                seen += 1
+    assert seen >= 30 and len(gold) == 40
