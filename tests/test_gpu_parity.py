@@ -612,3 +612,41 @@ def test_mode3_multi_destination_through_roles():
                                   time_scale=1_000_000, flags=flags, timeout_ms=20000)
         assert r["verified"] and r["ready_equals_assignment"]
         assert r["layers_checked"] == sum(len(v) for v in o.parse_config(text).assignment.values())
+
+
+def test_concurrent_sends_from_many_threads():
+    """Transport.Send is called from one goroutine per transfer (node.go:343, :598): the C ABI must take concurrent
+    dissem_send / dissem_wait / dissem_layer_alloc calls on one context."""
+    import threading
+    size = 2 * d.CHUNK_BYTES + 777
+    n_layers = 24
+    with d.Engine([0, 0, 0, 0]) as eng:
+        for l in range(n_layers):
+            eng.alloc(0, l, size)
+            eng.fill(0, l, d.FILL_PATTERN, SEED)
+        errors = []
+
+        def worker(l):
+            try:
+                dst = 1 + l % 3
+                eng.alloc(dst, l, size)                    # the receiver-side make(LayerData, n), transport.go:201
+                half = size // 2 + 5
+                t1 = eng.send(0, dst, l, 0, half, size)
+                t2 = eng.send(0, dst, l, half, size - half, size)
+                eng.wait(t2)
+                eng.wait(t1)
+            except Exception as e:                         # noqa: BLE001
+                errors.append((l, repr(e)))
+
+        threads = [threading.Thread(target=worker, args=(l,)) for l in range(n_layers)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=60)
+        assert not errors, errors
+        for l in range(n_layers):
+            want = o.fill_bytes(o.FILL_PATTERN, l, size, SEED)
+            dst = 1 + l % 3
+            assert np.array_equal(eng.read(dst, l), want), l
+            assert np.array_equal(eng.checksums(dst, l), o.checksum(want)), l
+            assert eng.received(dst, l) == size
