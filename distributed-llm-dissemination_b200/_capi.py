@@ -67,6 +67,11 @@ def load_library() -> ctypes.CDLL:
         "dissem_layer_attach_host": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
         "dissem_layer_export": (c.c_int, [P, c.c_int, c.c_int, P]),
         "dissem_layer_import": (c.c_int, [P, c.c_int, c.c_int, i64, P]),
+        "dissem_layer_export_fd": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(c.c_int)]),
+        "dissem_layer_import_fd": (c.c_int, [P, c.c_int, c.c_int, i64, c.c_int]),
+        "dissem_mcast_create": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.c_int)]),
+        "dissem_mcast_join": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(c.c_int), c.c_int, c.c_int, c.c_int]),
+        "dissem_mcast_bind": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(c.c_int), c.c_int]),
         "dissem_send": (c.c_int, [P, c.c_int, c.c_int, c.c_int, i64, i64, i64, c.POINTER(i64)]),
         "dissem_schedule_submit": (c.c_int, [P, c.POINTER(Xfer), c.c_int, c.POINTER(i64)]),
         "dissem_schedule_compile": (c.c_int, [P, c.POINTER(Xfer), c.c_int, c.POINTER(i64)]),
@@ -269,6 +274,29 @@ class Engine:
     def import_(self, node: int, layer: int, size: int, handle: bytes):
         buf = (ctypes.c_uint8 * 64).from_buffer_copy(handle)
         _check(lib().dissem_layer_import(self._ctx, node, layer, size, buf))
+
+    # ---- shareable VMM layers and cross-process multicast (file descriptors travel over a unix socket) ----
+    def export_fd(self, node: int, layer: int) -> int:
+        fd = ctypes.c_int(-1)
+        _check(lib().dissem_layer_export_fd(self._ctx, node, layer, ctypes.byref(fd)))
+        return fd.value
+
+    def import_fd(self, node: int, layer: int, size: int, fd: int):
+        _check(lib().dissem_layer_import_fd(self._ctx, node, layer, size, fd))
+
+    def mcast_create(self, layer: int, src: int, dsts: Sequence[int]) -> int:
+        arr = (ctypes.c_int * len(dsts))(*dsts)
+        fd = ctypes.c_int(-1)
+        _check(lib().dissem_mcast_create(self._ctx, layer, src, arr, len(dsts), ctypes.byref(fd)))
+        return fd.value
+
+    def mcast_join(self, layer: int, src: int, dsts: Sequence[int], my_node: int, fd: int):
+        arr = (ctypes.c_int * len(dsts))(*dsts)
+        _check(lib().dissem_mcast_join(self._ctx, layer, src, arr, len(dsts), my_node, fd))
+
+    def mcast_bind(self, layer: int, src: int, dsts: Sequence[int]):
+        arr = (ctypes.c_int * len(dsts))(*dsts)
+        _check(lib().dissem_mcast_bind(self._ctx, layer, src, arr, len(dsts)))
 
     # ---- transfers ----
     def send(self, src: int, dst: int, layer: int, off: int, size: int, total: int) -> int:

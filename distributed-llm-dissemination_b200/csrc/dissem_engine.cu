@@ -627,8 +627,8 @@ int dissem_close(dissem_ctx *ctx) {
             for (auto &kv : ctx->layers[n]) {
                 LayerBuf &lb = kv.second;
                 if (lb.host) continue;
-                if (lb.imported) cudaIpcCloseMemHandle(lb.base);
-                else if (lb.vmm) vmm_free(&lb.blk);
+                if (lb.vmm) vmm_free(&lb.blk);
+                else if (lb.imported) cudaIpcCloseMemHandle(lb.base);
                 else {
                     cudaSetDevice(lb.device);
                     cudaFree(lb.base);
@@ -663,7 +663,7 @@ int dissem_layer_alloc(dissem_ctx *ctx, int node, int layer, int64_t size) {
         // VMM-backed: can be bound to an NVLS multicast object; mapped for every local GPU (peer stores)
         std::vector<int> access;
         for (auto &d : ctx->devs) access.push_back(d.dev);
-        std::string err = vmm_alloc(ds->dev, access, (size_t)lb.alloc_bytes(), &lb.blk);
+        std::string err = vmm_alloc(ds->dev, access, (size_t)lb.alloc_bytes(), &lb.blk, ctx->opt_alloc_vmm == 2);
         if (!err.empty()) return set_error(DISSEM_ECUDA, "VMM allocation of layer %d on node %d: %s", layer, node, err.c_str());
         lb.vmm = true;
         lb.base = reinterpret_cast<uint8_t *>(lb.blk.va);
@@ -701,8 +701,8 @@ int dissem_layer_free(dissem_ctx *ctx, int node, int layer) {
         } else ++it;
     }
     if (lb->host) { /* caller-owned memory: nothing to release */ }
+    else if (lb->vmm) vmm_free(&lb->blk);                       // owned or imported through a file descriptor
     else if (lb->imported) CUDA_TRY(cudaIpcCloseMemHandle(lb->base));
-    else if (lb->vmm) vmm_free(&lb->blk);
     else {
         CUDA_TRY(cudaSetDevice(lb->device));
         CUDA_TRY(cudaFree(lb->base));
@@ -871,6 +871,108 @@ int dissem_layer_import(dissem_ctx *ctx, int node, int layer, int64_t size, cons
     lb.imported = true;
     lb.device = -1;
     ctx->layers[node][layer] = lb;
+    return DISSEM_OK;
+}
+
+int dissem_layer_export_fd(dissem_ctx *ctx, int node, int layer, int *fd_out) {
+    if (!ctx || !fd_out) return set_error(DISSEM_EINVAL, "dissem_layer_export_fd: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *lb = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    if (!lb->vmm || lb->imported) return set_error(DISSEM_EINVAL, "layer %d of node %d is not a locally owned shareable VMM layer (set alloc_vmm = 2 before allocating)", layer, node);
+    std::string err = vmm_export_fd(lb->blk, fd_out);
+    if (!err.empty()) return set_error(DISSEM_ECUDA, "%s", err.c_str());
+    return DISSEM_OK;
+}
+
+int dissem_layer_import_fd(dissem_ctx *ctx, int node, int layer, int64_t size, int fd) {
+    if (!ctx || fd < 0) return set_error(DISSEM_EINVAL, "dissem_layer_import_fd: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = check_node(ctx, node);
+    if (rc) return rc;
+    if (ctx->node_dev_slot[node] >= 0) return set_error(DISSEM_EINVAL, "node %d is local; import is for remote nodes", node);
+    if (ctx->layers[node].count(layer)) return set_error(DISSEM_EEXIST, "layer %d of node %d already imported", layer, node);
+    std::vector<int> access;
+    for (auto &d : ctx->devs) access.push_back(d.dev);
+    LayerBuf lb;
+    lb.size = size < 0 ? 0 : size;
+    std::string err = vmm_import_fd(fd, -1, access, (size_t)lb.alloc_bytes(), &lb.blk);
+    if (!err.empty()) return set_error(DISSEM_ECUDA, "%s", err.c_str());
+    lb.base = reinterpret_cast<uint8_t *>(lb.blk.va);
+    lb.imported = true;
+    lb.vmm = true;
+    lb.device = -1;
+    ctx->layers[node][layer] = lb;
+    return DISSEM_OK;
+}
+
+static std::pair<int, std::vector<int>> mcast_key(int layer, int src_node, const int *dst_nodes, int n_dst) {
+    std::vector<int> team{src_node};
+    std::vector<int> d(dst_nodes, dst_nodes + n_dst);
+    std::sort(d.begin(), d.end());
+    team.insert(team.end(), d.begin(), d.end());
+    return std::make_pair(layer, team);
+}
+
+int dissem_mcast_create(dissem_ctx *ctx, int layer, int src_node, const int *dst_nodes, int n_dst, int *fd_out) {
+    if (!ctx || !dst_nodes || n_dst < 1 || !fd_out) return set_error(DISSEM_EINVAL, "dissem_mcast_create: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *src = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, src_node, layer, &src);
+    if (rc) return rc;
+    rc = local_dev(ctx, src_node, &ds);
+    if (rc) return rc;
+    if (!src->vmm || src->imported) return set_error(DISSEM_EINVAL, "the source copy of layer %d is not a shareable VMM layer of this process", layer);
+    auto key = mcast_key(layer, src_node, dst_nodes, n_dst);
+    if (ctx->mcasts.count(key)) return set_error(DISSEM_EEXIST, "multicast object for layer %d already exists", layer);
+    McObject mc;
+    std::string err = mcast_create_shared(n_dst + 1, src->blk.bytes, ds->dev, &mc, fd_out);
+    if (!err.empty()) return set_error(DISSEM_ENOTSUP, "%s", err.c_str());
+    ctx->mcasts.emplace(key, mc);
+    return DISSEM_OK;
+}
+
+int dissem_mcast_join(dissem_ctx *ctx, int layer, int src_node, const int *dst_nodes, int n_dst, int my_node, int fd) {
+    if (!ctx || !dst_nodes || n_dst < 1 || fd < 0) return set_error(DISSEM_EINVAL, "dissem_mcast_join: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    LayerBuf *mine = nullptr;
+    DeviceState *ds = nullptr;
+    int rc = find_layer(ctx, my_node, layer, &mine);
+    if (rc) return rc;
+    rc = local_dev(ctx, my_node, &ds);
+    if (rc) return rc;
+    if (!mine->vmm || mine->imported) return set_error(DISSEM_EINVAL, "node %d's copy of layer %d is not a shareable VMM layer of this process", my_node, layer);
+    auto key = mcast_key(layer, src_node, dst_nodes, n_dst);
+    if (ctx->mcasts.count(key)) return set_error(DISSEM_EEXIST, "multicast object for layer %d already joined", layer);
+    McObject mc;
+    std::string err = mcast_join(fd, mine->blk.bytes, ds->dev, &mc);
+    if (!err.empty()) return set_error(DISSEM_ENOTSUP, "%s", err.c_str());
+    ctx->mcasts.emplace(key, mc);
+    return DISSEM_OK;
+}
+
+int dissem_mcast_bind(dissem_ctx *ctx, int layer, int src_node, const int *dst_nodes, int n_dst) {
+    if (!ctx || !dst_nodes || n_dst < 1) return set_error(DISSEM_EINVAL, "dissem_mcast_bind: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto key = mcast_key(layer, src_node, dst_nodes, n_dst);
+    auto it = ctx->mcasts.find(key);
+    if (it == ctx->mcasts.end() || !it->second.handle) return set_error(DISSEM_ENOENT, "no multicast object for layer %d: create or join it first", layer);
+    for (int node : key.second) {
+        if (ctx->node_dev_slot[node] < 0) continue;                   // another process binds that member
+        LayerBuf *lb = nullptr;
+        int rc = find_layer(ctx, node, layer, &lb);
+        if (rc) return rc;
+        if (!lb->vmm || lb->imported) return set_error(DISSEM_EINVAL, "node %d's copy of layer %d cannot be bound", node, layer);
+        std::string err = mcast_bind_block(&it->second, lb->blk);
+        if (!err.empty()) return set_error(DISSEM_ENOTSUP, "%s", err.c_str());
+    }
+    if (ctx->node_dev_slot[src_node] >= 0 && !it->second.valid()) {
+        std::vector<int> access{ctx->devs[ctx->node_dev_slot[src_node]].dev};
+        std::string err = mcast_map(&it->second, access);
+        if (!err.empty()) return set_error(DISSEM_ENOTSUP, "%s", err.c_str());
+    }
     return DISSEM_OK;
 }
 
@@ -1276,7 +1378,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     if (k == "ctas_per_sm") { if (value < 0 || value > 32) return set_error(DISSEM_EINVAL, "ctas_per_sm out of range"); ctx->opt_ctas_per_sm = value; }
     else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
     else if (k == "tma_cfg") { if (value < 0 || value > 5) return set_error(DISSEM_EINVAL, "tma_cfg must be 0..5"); ctx->opt_tma_cfg = value; }
-    else if (k == "alloc_vmm") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0 or 1"); ctx->opt_alloc_vmm = value; }
+    else if (k == "alloc_vmm") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0, 1 or 2"); ctx->opt_alloc_vmm = value; }
     else if (k == "mcast") { if (value < 0 || value > 3) return set_error(DISSEM_EINVAL, "mcast must be 0..3"); ctx->opt_mcast = value; }
     else if (k == "pull") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "pull must be 0, 1 or 2"); ctx->opt_pull = value; }
     else if (k == "reg_cfg") { if (value < 0 || value > 9) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..9"); ctx->opt_reg_cfg = value; }

@@ -21,6 +21,8 @@ struct DriverApi {
     CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
     CUresult (*MemUnmap)(CUdeviceptr, size_t) = nullptr;
     CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
+    CUresult (*MemExportToShareableHandle)(void *, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long) = nullptr;
+    CUresult (*MemImportFromShareableHandle)(CUmemGenericAllocationHandle *, void *, CUmemAllocationHandleType) = nullptr;
     CUresult (*MulticastCreate)(CUmemGenericAllocationHandle *, const CUmulticastObjectProp *) = nullptr;
     CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
     CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long) = nullptr;
@@ -55,6 +57,8 @@ const DriverApi &driver() {
                  resolve("cuMemAddressReserve", &api.MemAddressReserve, &e) &&
                  resolve("cuMemAddressFree", &api.MemAddressFree, &e) && resolve("cuMemMap", &api.MemMap, &e) &&
                  resolve("cuMemUnmap", &api.MemUnmap, &e) && resolve("cuMemSetAccess", &api.MemSetAccess, &e) &&
+                 resolve("cuMemExportToShareableHandle", &api.MemExportToShareableHandle, &e) &&
+                 resolve("cuMemImportFromShareableHandle", &api.MemImportFromShareableHandle, &e) &&
                  resolve("cuMulticastCreate", &api.MulticastCreate, &e) &&
                  resolve("cuMulticastAddDevice", &api.MulticastAddDevice, &e) &&
                  resolve("cuMulticastBindMem", &api.MulticastBindMem, &e) &&
@@ -73,14 +77,23 @@ std::string cu_err(const char *what, CUresult r) {
     return std::string(what) + ": " + (s ? s : "unknown driver error") + " (" + std::to_string((int)r) + ")";
 }
 
-CUmemAllocationProp alloc_prop(int device) {
+CUmemAllocationProp alloc_prop(int device, bool shareable = false) {
     CUmemAllocationProp p;
     memset(&p, 0, sizeof p);
     p.type = CU_MEM_ALLOCATION_TYPE_PINNED;
     p.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
     p.location.id = device;
-    p.requestedHandleTypes = CU_MEM_HANDLE_TYPE_NONE;
+    p.requestedHandleTypes = shareable ? CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR : CU_MEM_HANDLE_TYPE_NONE;
     return p;
+}
+
+size_t round_to_granularity(int device, bool shareable, size_t bytes, size_t *gran_out) {
+    CUmemAllocationProp prop = alloc_prop(device, shareable);
+    size_t gran = 0;
+    if (driver().MemGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS) gran = 0;
+    if (gran < (2u << 20)) gran = 2u << 20;
+    if (gran_out) *gran_out = gran;
+    return (bytes + gran - 1) / gran * gran;
 }
 
 std::string set_access(CUdeviceptr va, size_t bytes, const std::vector<int> &devices) {
@@ -97,19 +110,16 @@ std::string set_access(CUdeviceptr va, size_t bytes, const std::vector<int> &dev
 
 }  // namespace
 
-std::string vmm_alloc(int device, const std::vector<int> &access_devices, size_t bytes, VmmBlock *out) {
+std::string vmm_alloc(int device, const std::vector<int> &access_devices, size_t bytes, VmmBlock *out, bool shareable) {
     const DriverApi &d = driver();
     if (!d.ok) return d.err;
     cudaSetDevice(device);
     cudaFree(0);                                   // make sure the primary context exists
-    CUmemAllocationProp prop = alloc_prop(device);
+    CUmemAllocationProp prop = alloc_prop(device, shareable);
     size_t gran = 0;
-    CUresult r = d.MemGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED);
-    if (r != CUDA_SUCCESS) return cu_err("cuMemGetAllocationGranularity", r);
-    if (gran < (2u << 20)) gran = 2u << 20;
-    const size_t size = (bytes + gran - 1) / gran * gran;
+    const size_t size = round_to_granularity(device, shareable, bytes, &gran);
     CUmemGenericAllocationHandle h = 0;
-    r = d.MemCreate(&h, size, &prop, 0);
+    CUresult r = d.MemCreate(&h, size, &prop, 0);
     if (r != CUDA_SUCCESS) return cu_err("cuMemCreate", r);
     CUdeviceptr va = 0;
     r = d.MemAddressReserve(&va, size, gran, 0, 0);
@@ -122,6 +132,41 @@ std::string vmm_alloc(int device, const std::vector<int> &access_devices, size_t
     out->va = va;
     out->bytes = size;
     out->device = device;
+    return std::string();
+}
+
+std::string vmm_export_fd(const VmmBlock &b, int *fd_out) {
+    const DriverApi &d = driver();
+    if (!d.ok) return d.err;
+    int fd = -1;
+    CUresult r = d.MemExportToShareableHandle(&fd, b.handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+    if (r != CUDA_SUCCESS) return cu_err("cuMemExportToShareableHandle", r);
+    *fd_out = fd;
+    return std::string();
+}
+
+std::string vmm_import_fd(int fd, int owner_device, const std::vector<int> &access_devices, size_t bytes, VmmBlock *out) {
+    const DriverApi &d = driver();
+    if (!d.ok) return d.err;
+    if (access_devices.empty()) return "no local device to map the block on";
+    cudaSetDevice(access_devices[0]);
+    cudaFree(0);
+    size_t gran = 0;
+    const size_t size = round_to_granularity(access_devices[0], true, bytes, &gran);
+    CUmemGenericAllocationHandle h = 0;
+    CUresult r = d.MemImportFromShareableHandle(&h, (void *)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+    if (r != CUDA_SUCCESS) return cu_err("cuMemImportFromShareableHandle", r);
+    CUdeviceptr va = 0;
+    r = d.MemAddressReserve(&va, size, gran, 0, 0);
+    if (r != CUDA_SUCCESS) { d.MemRelease(h); return cu_err("cuMemAddressReserve", r); }
+    r = d.MemMap(va, size, 0, h, 0);
+    if (r != CUDA_SUCCESS) { d.MemAddressFree(va, size); d.MemRelease(h); return cu_err("cuMemMap(imported)", r); }
+    std::string e = set_access(va, size, access_devices);
+    if (!e.empty()) { d.MemUnmap(va, size); d.MemAddressFree(va, size); d.MemRelease(h); return e; }
+    out->handle = h;
+    out->va = va;
+    out->bytes = size;
+    out->device = owner_device;
     return std::string();
 }
 
@@ -210,11 +255,86 @@ std::string mcast_create(const std::vector<int> &devices, const std::vector<cons
     return std::string();
 }
 
+std::string mcast_create_shared(int n_devices, size_t bytes, int own_device, McObject *m, int *fd_out) {
+    const DriverApi &d = driver();
+    if (!d.ok) return d.err;
+    cudaSetDevice(own_device);
+    cudaFree(0);
+    CUmulticastObjectProp prop;
+    memset(&prop, 0, sizeof prop);
+    prop.numDevices = (unsigned)n_devices;
+    prop.size = bytes;
+    prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    size_t gran_min = 0;
+    CUresult r = d.MulticastGetGranularity(&gran_min, &prop, CU_MULTICAST_GRANULARITY_MINIMUM);
+    if (r != CUDA_SUCCESS) return cu_err("cuMulticastGetGranularity", r);
+    if (gran_min && bytes % gran_min) return "block size is not a multiple of the multicast granularity";
+    CUmemGenericAllocationHandle mc = 0;
+    r = d.MulticastCreate(&mc, &prop);
+    if (r != CUDA_SUCCESS) return cu_err("cuMulticastCreate(shareable)", r);
+    CUdevice cd;
+    r = d.DeviceGet(&cd, own_device);
+    if (r == CUDA_SUCCESS) r = d.MulticastAddDevice(mc, cd);
+    if (r != CUDA_SUCCESS) { d.MemRelease(mc); return cu_err("cuMulticastAddDevice", r); }
+    int fd = -1;
+    r = d.MemExportToShareableHandle(&fd, mc, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+    if (r != CUDA_SUCCESS) { d.MemRelease(mc); return cu_err("cuMemExportToShareableHandle(multicast)", r); }
+    m->handle = mc;
+    m->va = 0;
+    m->bytes = bytes;
+    m->devices.assign(1, own_device);
+    *fd_out = fd;
+    return std::string();
+}
+
+std::string mcast_join(int fd, size_t bytes, int own_device, McObject *m) {
+    const DriverApi &d = driver();
+    if (!d.ok) return d.err;
+    cudaSetDevice(own_device);
+    cudaFree(0);
+    CUmemGenericAllocationHandle mc = 0;
+    CUresult r = d.MemImportFromShareableHandle(&mc, (void *)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+    if (r != CUDA_SUCCESS) return cu_err("cuMemImportFromShareableHandle(multicast)", r);
+    CUdevice cd;
+    r = d.DeviceGet(&cd, own_device);
+    if (r == CUDA_SUCCESS) r = d.MulticastAddDevice(mc, cd);
+    if (r != CUDA_SUCCESS) { d.MemRelease(mc); return cu_err("cuMulticastAddDevice(joined)", r); }
+    m->handle = mc;
+    m->va = 0;
+    m->bytes = bytes;
+    m->devices.assign(1, own_device);
+    return std::string();
+}
+
+std::string mcast_bind_block(McObject *m, const VmmBlock &b) {
+    const DriverApi &d = driver();
+    if (!d.ok) return d.err;
+    if (b.bytes != m->bytes) return "multicast block size mismatch";
+    CUresult r = d.MulticastBindMem(m->handle, 0, b.handle, 0, m->bytes, 0);
+    return r == CUDA_SUCCESS ? std::string() : cu_err("cuMulticastBindMem", r);
+}
+
+std::string mcast_map(McObject *m, const std::vector<int> &access_devices) {
+    const DriverApi &d = driver();
+    if (!d.ok) return d.err;
+    CUdeviceptr va = 0;
+    CUresult r = d.MemAddressReserve(&va, m->bytes, 2u << 20, 0, 0);
+    if (r != CUDA_SUCCESS) return cu_err("cuMemAddressReserve(multicast)", r);
+    r = d.MemMap(va, m->bytes, 0, m->handle, 0);
+    if (r != CUDA_SUCCESS) { d.MemAddressFree(va, m->bytes); return cu_err("cuMemMap(multicast)", r); }
+    std::string e = set_access(va, m->bytes, access_devices);
+    if (!e.empty()) { d.MemUnmap(va, m->bytes); d.MemAddressFree(va, m->bytes); return e; }
+    m->va = va;
+    return std::string();
+}
+
 void mcast_destroy(McObject *m) {
     const DriverApi &d = driver();
-    if (!d.ok || !m->valid()) return;
-    d.MemUnmap(m->va, m->bytes);
-    d.MemAddressFree(m->va, m->bytes);
+    if (!d.ok || !m->handle) return;
+    if (m->va) {
+        d.MemUnmap(m->va, m->bytes);
+        d.MemAddressFree(m->va, m->bytes);
+    }
     for (int dev : m->devices) {
         CUdevice cd;
         if (d.DeviceGet(&cd, dev) == CUDA_SUCCESS) d.MulticastUnbind(m->handle, cd, 0, m->bytes);

@@ -28,7 +28,12 @@ struct McObject {
 };
 
 // Empty string on success, else what failed.
-std::string vmm_alloc(int device, const std::vector<int> &access_devices, size_t bytes, VmmBlock *out);
+// shareable: the allocation can be exported as a POSIX file descriptor (and bound to a shareable multicast object)
+std::string vmm_alloc(int device, const std::vector<int> &access_devices, size_t bytes, VmmBlock *out, bool shareable = false);
+// A file descriptor for the block, to be passed to another process (SCM_RIGHTS); the caller closes its copy.
+std::string vmm_export_fd(const VmmBlock &b, int *fd_out);
+// Map a block exported by another process; `bytes` as the exporter allocated it (rounded the same way).
+std::string vmm_import_fd(int fd, int owner_device, const std::vector<int> &access_devices, size_t bytes, VmmBlock *out);
 void vmm_free(VmmBlock *b);
 
 // Does every device support multicast objects (CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED)?
@@ -36,5 +41,13 @@ bool mcast_supported(const std::vector<int> &devices, std::string *why);
 // blocks[i] lives on devices[i]; all have the same size.  The object is mapped for access from every device listed.
 std::string mcast_create(const std::vector<int> &devices, const std::vector<const VmmBlock *> &blocks, McObject *out);
 void mcast_destroy(McObject *m);
+
+// One process per GPU.  The source's process creates the object for `n_devices` members, adds its own device and exports a
+// file descriptor; every other member's process joins (imports the fd, adds its device).  After ALL members joined, each
+// process binds its own block; the source's process also maps the object.  `m->devices` lists only the LOCAL devices.
+std::string mcast_create_shared(int n_devices, size_t bytes, int own_device, McObject *m, int *fd_out);
+std::string mcast_join(int fd, size_t bytes, int own_device, McObject *m);
+std::string mcast_bind_block(McObject *m, const VmmBlock &b);
+std::string mcast_map(McObject *m, const std::vector<int> &access_devices);
 
 }  // namespace dissem

@@ -108,3 +108,74 @@ class RoundedSchedule:
         for s in self.scheds:
             self.eng.sched_free(s)
         self.scheds = []
+
+
+class FdExchange:
+    """Passes file descriptors (shareable VMM / multicast handles) between the ranks of one box over unix sockets
+    (SCM_RIGHTS).  Plumbing only.  Every descriptor travels with a text key; recv(key) blocks until it has arrived."""
+
+    def __init__(self, rank: int, tag: str):
+        import os
+        import socket
+        import threading
+        self._socket, self._os = socket, os
+        self.rank, self.tag = rank, tag
+        self.path = self._path(rank)
+        try:
+            os.unlink(self.path)
+        except FileNotFoundError:
+            pass
+        self._srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        self._srv.bind(self.path)
+        self._srv.listen(256)
+        self._got: Dict[str, int] = {}
+        self._cv = threading.Condition()
+        self._stop = False
+        self._thr = threading.Thread(target=self._serve, daemon=True)
+        self._thr.start()
+
+    def _path(self, rank: int) -> str:
+        return f"/tmp/dissem-{self.tag}-{rank}.sock"
+
+    def _serve(self):
+        while not self._stop:
+            try:
+                conn, _ = self._srv.accept()
+            except OSError:
+                return
+            with conn:
+                msg, fds, _flags, _addr = self._socket.recv_fds(conn, 4096, 8)
+                if fds:
+                    with self._cv:
+                        self._got[msg.decode()] = fds[0]
+                        self._cv.notify_all()
+
+    def send(self, to_rank: int, key: str, fd: int, keep: bool = False):
+        import time
+        s = self._socket.socket(self._socket.AF_UNIX, self._socket.SOCK_STREAM)
+        for _ in range(200):
+            try:
+                s.connect(self._path(to_rank))
+                break
+            except (FileNotFoundError, ConnectionRefusedError):
+                time.sleep(0.05)
+        else:
+            raise RuntimeError(f"rank {to_rank} is not listening for descriptors")
+        with s:
+            self._socket.send_fds(s, [key.encode()], [fd])
+        if not keep:
+            self._os.close(fd)
+
+    def recv(self, key: str, timeout: float = 60.0) -> int:
+        with self._cv:
+            if not self._cv.wait_for(lambda: key in self._got, timeout=timeout):
+                raise TimeoutError(f"descriptor {key!r} never arrived at rank {self.rank}")
+            return self._got.pop(key)
+
+    def close(self):
+        self._stop = True
+        try:
+            self._srv.close()
+            self._os.unlink(self.path)
+        except OSError:
+            pass

@@ -120,6 +120,21 @@ int dissem_layer_export(dissem_ctx *ctx, int node, int layer, uint8_t handle_out
 /* Map a remote node's layer (allocated by its owner process) so that local nodes can push into it. */
 int dissem_layer_import(dissem_ctx *ctx, int node, int layer, int64_t size, const uint8_t handle[64]);
 
+/* The same for layers allocated with the VMM API ("alloc_vmm" = 2: shareable), which NVLS multicast needs: the handle
+ * is a POSIX file descriptor that the host side passes to the peer process (SCM_RIGHTS on a unix socket) and closes. */
+int dissem_layer_export_fd(dissem_ctx *ctx, int node, int layer, int *fd_out);
+int dissem_layer_import_fd(dissem_ctx *ctx, int node, int layer, int64_t size, int fd);
+/* NVLS multicast with one process per GPU, for the transfers of `layer` from src_node to dst_nodes[0..n_dst):
+ *   1. the source's process:      dissem_mcast_create -> fd, sent to every destination's process;
+ *   2. each destination process:  dissem_mcast_join(fd) with my_node = its member node;
+ *   3. after ALL members have joined (a barrier of the host side), every member process: dissem_mcast_bind.
+ * A later dissem_schedule_* call in the source's process that carries those transfers then uses the object
+ * (subject to the "mcast" option).  Every member's copy, the source's included, must be a shareable VMM layer, and
+ * the source's process must have imported the destinations' copies (dissem_layer_import_fd). */
+int dissem_mcast_create(dissem_ctx *ctx, int layer, int src_node, const int *dst_nodes, int n_dst, int *fd_out);
+int dissem_mcast_join(dissem_ctx *ctx, int layer, int src_node, const int *dst_nodes, int n_dst, int my_node, int fd);
+int dissem_mcast_bind(dissem_ctx *ctx, int layer, int src_node, const int *dst_nodes, int n_dst);
+
 /* ---- the hot path: TcpTransport.Send layer branch + sendLayerMsg + writeWithLimit on the sender
  *      (transport.go:258-275, :308-373, :407-424) and handleIncomingMsg layer branch on the receiver
  *      (transport.go:127-224), as one push kernel per source GPU with the checksum fused in ----------- */
@@ -213,7 +228,7 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
  * 3 512x8, 4 1024x4, 5 1024x2, 6 512x2; 7/8/9 = 512x2, 512x4, 256x4 with 32-byte loads and stores),
  * "tma_cfg" (TMA ring shape, stage bytes x stages: 0 16Kx6 (default), 1 32Kx3, 2 8Kx12, 3 16Kx4, 4 8Kx6, 5 4Kx12),
  * "alloc_vmm" (1 = dissem_layer_alloc uses the VMM API so that layers can be bound to NVLS multicast objects;
- *  such layers cannot be exported to other processes yet),
+ *  2 = the same, shareable with other processes through dissem_layer_export_fd),
  * "mcast" (transfers of the same bytes from one source to several GPUs can go as ONE NVLS multicast store stream
  *  when every buffer involved is VMM-backed and local.  1 (default) = do so when a cost model built on the measured
  *  port rates says the plan gets shorter (i.e. it is bound by a source's egress); 3 = always; 0 = never (unicast

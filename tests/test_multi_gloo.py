@@ -94,3 +94,31 @@ def test_pull_flags_swap_exports_and_imports():
     # the leader exports the SOURCE layers that are pulled from it, and imports nothing for them
     assert {(n, l) for (n, l, _t) in multi.exports_needed(xf, owner, 0)} == {(0, x.layer) for x in pulled}
     assert sum(len(multi.my_transfers(xf, owner, r)) for r in range(8)) == len(xf)
+
+
+def _fd_sender(tag, path):
+    fx = multi.FdExchange(1, tag)
+    fd = os.open(path, os.O_RDONLY)
+    fx.send(0, "buf:1:7", fd)
+    fx.close()
+
+
+def test_fd_exchange_passes_descriptors_between_processes(tmp_path):
+    """The plumbing that carries shareable VMM / multicast handles between ranks (SCM_RIGHTS on unix sockets)."""
+    p = tmp_path / "payload"
+    p.write_bytes(b"layer bytes travel as descriptors")
+    tag = f"test{os.getpid()}"
+    fx = multi.FdExchange(0, tag)
+    try:
+        ctx = mp.get_context("spawn")
+        child = ctx.Process(target=_fd_sender, args=(tag, str(p)))
+        child.start()
+        fd = fx.recv("buf:1:7", timeout=60)
+        child.join(timeout=60)
+        assert child.exitcode == 0
+        assert os.read(fd, 100) == b"layer bytes travel as descriptors"
+        os.close(fd)
+        with pytest.raises(TimeoutError):
+            fx.recv("never", timeout=0.2)
+    finally:
+        fx.close()
