@@ -263,7 +263,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                     y.size == x.size && y.total == x.total && y.dst_node != x.dst_node)
                     g.members.push_back(j);
             }
-            const bool forced_single = ctx->opt_mcast == 2 && ctx->node_dev_slot[x.dst_node] >= 0 && ctx->node_dev_slot[x.dst_node] != sslot;
+            const bool forced_single = ctx->opt_mcast == 2 && ctx->node_dev_slot[x.dst_node] != sslot;   // another GPU, possibly another process
             if (g.members.size() < 2 && !forced_single) continue;
             for (int m : g.members) grouped[m] = 1;
             groups.push_back(std::move(g));
