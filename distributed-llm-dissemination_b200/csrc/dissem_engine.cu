@@ -841,7 +841,7 @@ int dissem_layer_export(dissem_ctx *ctx, int node, int layer, uint8_t handle_out
     if (rc) return rc;
     if (lb->imported) return set_error(DISSEM_EINVAL, "layer %d of node %d is itself imported", layer, node);
     if (lb->host) return set_error(DISSEM_ENOTSUP, "layer %d of node %d is attached host memory; peers read pinned host memory of their own process only", layer, node);
-    if (lb->vmm) return set_error(DISSEM_ENOTSUP, "layer %d of node %d is VMM-backed (alloc_vmm); cross-process export of such layers is not implemented", layer, node);
+    if (lb->vmm) return set_error(DISSEM_ENOTSUP, "layer %d of node %d is VMM-backed (alloc_vmm): export it with dissem_layer_export_fd", layer, node);
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     cudaIpcMemHandle_t h;
     CUDA_TRY(cudaSetDevice(lb->device));
