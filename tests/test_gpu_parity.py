@@ -650,3 +650,40 @@ def test_concurrent_sends_from_many_threads():
             assert np.array_equal(eng.read(dst, l), want), l
             assert np.array_equal(eng.checksums(dst, l), o.checksum(want)), l
             assert eng.received(dst, l) == size
+
+
+def test_shareable_vmm_layers_cross_context_via_fd():
+    """dissem_layer_export_fd / import_fd: two contexts stand for two processes (an fd is valid as is inside one process).
+    Context A owns node 0, context B owns node 1; A pushes into B's buffer and pulls are B's business."""
+    size = 4 * d.CHUNK_BYTES + 160
+    dev_b = 1 if _n_gpus() >= 2 else 0
+    with d.Engine([0, -1]) as a, d.Engine([-1, dev_b]) as b:
+        for e in (a, b):
+            e.set_option("alloc_vmm", 2)
+        a.alloc(0, 3, size)
+        a.fill(0, 3, d.FILL_PATTERN, SEED)
+        b.alloc(1, 3, size)
+        b.fill(1, 3, d.FILL_POISON)
+        fd = b.export_fd(1, 3)
+        a.import_fd(1, 3, size, fd)
+        os.close(fd)
+        with pytest.raises(d.DissemError):
+            a.export(0, 3)                                   # the 64-byte IPC form does not apply to VMM layers
+        a.wait(a.send(0, 1, 3, 0, size, size))
+        want = o.fill_bytes(o.FILL_PATTERN, 3, size, SEED)
+        assert np.array_equal(b.read(1, 3), want)
+        assert np.array_equal(b.checksums(1, 3), o.checksum(want)) and b.received(1, 3) == size
+        if dev_b == 1:
+            # NVLS across the two contexts: create in A, join in B, bind in both, then A's send goes through the object
+            mfd = a.mcast_create(3, 0, [1])
+            b.mcast_join(3, 0, [1], 1, mfd)
+            os.close(mfd)
+            a.mcast_bind(3, 0, [1])
+            b.mcast_bind(3, 0, [1])
+            b.fill(1, 3, d.FILL_POISON)
+            b.reset(1, 3)
+            a.set_option("mcast", 2)
+            before = a.get_option("mcast_groups")
+            a.wait(a.send(0, 1, 3, 0, size, size))
+            assert a.get_option("mcast_groups") == before + 1
+            assert np.array_equal(b.read(1, 3), want) and np.array_equal(b.checksums(1, 3), o.checksum(want))
