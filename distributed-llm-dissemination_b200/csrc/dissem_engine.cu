@@ -1063,151 +1063,6 @@ int dissem_send(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t 
     return dissem_schedule_submit(ctx, &x, 1, out);
 }
 
-int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, int n_nodes) {
-    if (n < 0 || (n > 0 && !xfers) || !gpu_of_node || n_nodes <= 0) return set_error(DISSEM_EINVAL, "dissem_plan_directions: bad arguments");
-    std::map<int, int64_t> egress, ingress;
-    for (int i = 0; i < n; ++i) {
-        const dissem_xfer &x = xfers[i];
-        if (x.src_node < 0 || x.src_node >= n_nodes || x.dst_node < 0 || x.dst_node >= n_nodes)
-            return set_error(DISSEM_ENOENT, "transfer %d names a node outside [0,%d)", i, n_nodes);
-        const int gs = gpu_of_node[x.src_node], gd = gpu_of_node[x.dst_node];
-        if (gs == gd) continue;
-        egress[gs] += x.size;
-        ingress[gd] += x.size;
-    }
-    for (int i = 0; i < n; ++i) {
-        dissem_xfer &x = xfers[i];
-        const int gs = gpu_of_node[x.src_node], gd = gpu_of_node[x.dst_node];
-        x.flags &= ~DISSEM_XFER_PULL;
-        if (gs == gd) continue;
-        const int64_t forward = std::max(egress[gs], ingress[gd]);
-        const int64_t reverse = std::max(ingress[gs], egress[gd]);
-        if (2 * reverse < forward) x.flags |= DISSEM_XFER_PULL;
-    }
-    return DISSEM_OK;
-}
-
-int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **out, int *n_out) {
-    if (n < 0 || (n > 0 && !in) || !out || !n_out || pieces < 1 || pieces > 4096)
-        return set_error(DISSEM_EINVAL, "dissem_plan_relay: bad arguments");
-    std::vector<dissem_xfer> res;
-    std::vector<char> used((size_t)std::max(n, 1), 0);
-    auto emit = [&](int src, int dst, const dissem_xfer &x, int hop) {
-        // pieces are cut at multiples of the checksum chunk in LAYER space, so every piece owns whole chunks
-        int64_t piece = (x.size + pieces - 1) / pieces;
-        piece = (piece + DISSEM_CHUNK_BYTES - 1) / DISSEM_CHUNK_BYTES * DISSEM_CHUNK_BYTES;
-        if (piece <= 0) piece = DISSEM_CHUNK_BYTES;
-        int64_t pos = x.off;
-        const int64_t end = x.off + x.size;
-        for (int p = 0; pos < end; ++p) {
-            int64_t stop = (pos / piece + 1) * piece;            // next piece boundary in layer space
-            if (stop > end) stop = end;
-            dissem_xfer y = x;
-            y.src_node = src;
-            y.dst_node = dst;
-            y.off = pos;
-            y.size = stop - pos;
-            y.flags = (x.flags & ~(0xFFFF << DISSEM_XFER_ROUND_SHIFT) & ~DISSEM_XFER_PULL) | DISSEM_XFER_ROUND(p + hop);
-            res.push_back(y);
-            pos = stop;
-        }
-    };
-    for (int i = 0; i < n; ++i) {
-        if (used[i]) continue;
-        const dissem_xfer &x = in[i];
-        used[i] = 1;
-        if (x.size <= 0) { res.push_back(x); continue; }
-        std::vector<int> dsts{x.dst_node};
-        for (int j = i + 1; j < n; ++j) {
-            const dissem_xfer &y = in[j];
-            if (!used[j] && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
-                y.total == x.total && y.dst_node != x.dst_node) {
-                dsts.push_back(y.dst_node);
-                used[j] = 1;
-            }
-        }
-        std::sort(dsts.begin(), dsts.end());
-        // rotate so that the first hop (which forwards the most) is not always the same node
-        std::rotate(dsts.begin(), dsts.begin() + (size_t)((unsigned)x.layer % dsts.size()), dsts.end());
-        int prev = x.src_node;
-        for (size_t h = 0; h < dsts.size(); ++h) {
-            emit(prev, dsts[h], x, (int)h);                      // hop h forwards in round p+h what arrived in round p+h-1
-            prev = dsts[h];
-        }
-    }
-    dissem_xfer *buf = (dissem_xfer *)malloc(std::max<size_t>(res.size(), 1) * sizeof(dissem_xfer));
-    if (!buf) return set_error(DISSEM_ENOMEM, "out of memory");
-    memcpy(buf, res.data(), res.size() * sizeof(dissem_xfer));
-    *out = buf;
-    *n_out = (int)res.size();
-    return DISSEM_OK;
-}
-
-int dissem_plan_optimize(const dissem_xfer *in, int n, const int *gpu_of_node, int n_nodes, dissem_xfer **out, int *n_out,
-                         int *relay_pieces_out) {
-    if (n < 0 || (n > 0 && !in) || !gpu_of_node || n_nodes <= 0 || !out || !n_out)
-        return set_error(DISSEM_EINVAL, "dissem_plan_optimize: bad arguments");
-    for (int i = 0; i < n; ++i)
-        if (in[i].src_node < 0 || in[i].src_node >= n_nodes || in[i].dst_node < 0 || in[i].dst_node >= n_nodes)
-            return set_error(DISSEM_ENOENT, "transfer %d names a node outside [0,%d)", i, n_nodes);
-    // busiest-port bytes of a transfer list (transfers inside one GPU do not use a port)
-    auto busiest = [&](const dissem_xfer *xs, int cnt) {
-        std::map<int, int64_t> eg, ing;
-        for (int i = 0; i < cnt; ++i) {
-            const int gs = gpu_of_node[xs[i].src_node], gd = gpu_of_node[xs[i].dst_node];
-            if (gs == gd) continue;
-            eg[gs] += xs[i].size;
-            ing[gd] += xs[i].size;
-        }
-        int64_t m = 0;
-        for (auto &kv : eg) m = std::max(m, kv.second);
-        for (auto &kv : ing) m = std::max(m, kv.second);
-        return m;
-    };
-    // are there transfers of the same bytes from one source to several GPUs at all?
-    bool fanout = false;
-    int64_t biggest = 0;
-    for (int i = 0; i < n && !fanout; ++i)
-        for (int j = i + 1; j < n; ++j)
-            if (in[j].src_node == in[i].src_node && in[j].layer == in[i].layer && in[j].off == in[i].off &&
-                in[j].size == in[i].size && gpu_of_node[in[j].dst_node] != gpu_of_node[in[i].dst_node]) { fanout = true; break; }
-    for (int i = 0; i < n; ++i) biggest = std::max(biggest, in[i].size);
-    dissem_xfer *chosen = nullptr;
-    int n_chosen = 0, pieces_used = 0;
-    if (fanout && biggest >= (8ll << 20)) {
-        // relay chains: the source sends once, destinations forward; costs (pieces + hops - 1) / pieces in pipeline fill.
-        // Pieces of ~64 MiB keep a round long enough to hide its launch and barrier costs (profiles/r01_summary.md).
-        int pieces = (int)std::min<int64_t>(32, std::max<int64_t>(4, biggest / (64ll << 20)));
-        dissem_xfer *relay = nullptr;
-        int n_relay = 0;
-        int rc = dissem_plan_relay(in, n, pieces, &relay, &n_relay);
-        if (rc) return rc;
-        int max_round = 0;
-        for (int i = 0; i < n_relay; ++i) max_round = std::max(max_round, (relay[i].flags >> DISSEM_XFER_ROUND_SHIFT) & 0xFFFF);
-        const double t_uni = (double)busiest(in, n);
-        const double t_relay = (double)busiest(relay, n_relay) * (double)(max_round + 1) / (double)pieces;
-        if (t_relay < 0.9 * t_uni) {
-            chosen = relay;
-            n_chosen = n_relay;
-            pieces_used = pieces;
-        } else {
-            free(relay);
-        }
-    }
-    if (!chosen) {
-        chosen = (dissem_xfer *)malloc(std::max<size_t>((size_t)n, 1) * sizeof(dissem_xfer));
-        if (!chosen) return set_error(DISSEM_ENOMEM, "out of memory");
-        memcpy(chosen, in, (size_t)n * sizeof(dissem_xfer));
-        n_chosen = n;
-    }
-    int rc = dissem_plan_directions(chosen, n_chosen, gpu_of_node, n_nodes);
-    if (rc) { free(chosen); return rc; }
-    *out = chosen;
-    *n_out = n_chosen;
-    if (relay_pieces_out) *relay_pieces_out = pieces_used;
-    return DISSEM_OK;
-}
-
 int dissem_node_device(dissem_ctx *ctx, int node, int *device_out) {
     if (!ctx || !device_out) return set_error(DISSEM_EINVAL, "dissem_node_device: bad arguments");
     std::lock_guard<std::mutex> lk(ctx->mu);
