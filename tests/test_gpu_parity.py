@@ -687,3 +687,31 @@ def test_shareable_vmm_layers_cross_context_via_fd():
             a.wait(a.send(0, 1, 3, 0, size, size))
             assert a.get_option("mcast_groups") == before + 1
             assert np.array_equal(b.read(1, 3), want) and np.array_equal(b.checksums(1, 3), o.checksum(want))
+
+
+def test_layer_beyond_4GiB_offsets():
+    """The reference's own deployment config uses 10.9 GB layers (conf/config.json:15): byte offsets, word indices and
+    chunk numbers must survive 2^32.  One layer of 4 GiB + 3 chunks + 20 bytes: copy, fused table and re-read against the
+    C oracle; bytes around the 2^32 boundary and at the ragged end compared directly."""
+    size = (1 << 32) + 3 * d.CHUNK_BYTES + 20
+    import torch
+    if torch.cuda.mem_get_info(0)[0] < 3 * size:
+        pytest.skip("not enough free HBM")
+    data = co.fill_bytes(o.FILL_PATTERN, 2, size, SEED)
+    want = co.checksum(data)
+    with d.Engine([0, 0]) as eng:
+        eng.alloc(0, 2, size)
+        eng.fill(0, 2, d.FILL_PATTERN, SEED)
+        eng.alloc(1, 2, size)
+        eng.fill(1, 2, d.FILL_POISON)
+        # two fragments that meet just past 2^32, at an odd byte
+        cut = (1 << 32) + 5
+        eng.wait(eng.submit([(0, 1, 2, 0, cut, size), (0, 1, 2, cut, size - cut, size)]))
+        fused = eng.checksums(1, 2)
+        assert fused.shape == want.shape
+        assert np.array_equal(fused, want)
+        assert np.array_equal(eng.verify(1, 2), want)
+        assert eng.received(1, 2) == size
+        lo = (1 << 32) - 4096
+        assert np.array_equal(eng.read(1, 2, off=lo, size=8192), data[lo:lo + 8192])
+        assert np.array_equal(eng.read(1, 2, off=size - 4096, size=4096), data[-4096:])
