@@ -42,7 +42,24 @@ def readme_config():
         "Assignment": {"1": {"1": {}}, "2": {"1": {}, "3": {}}, "3": {"3": {}}}, "LayerSize": 1048576})
 
 
+def reference_conf_json():
+    """The reference's shipped conf/config.json (nested schema): nodes 0-6 each hold layers 0-7 of 10 930 691 768 B under
+    source "1" (209 715 200 B/s), node 7 holds nothing and is assigned all eight; NetworkBW 1 562 500 000 everywhere."""
+    size = 10_930_691_768
+    nodes = []
+    for i in range(8):
+        nd = {"Id": i, "Addr": f":{8080 + i}", "NetworkBW": 1_562_500_000, "IsLeader": i == 0}
+        if i < 7:
+            nd["Sources"] = {"0": 16_257_500, "1": 209_715_200}
+            nd["InitialLayers"] = {"1": {str(l): {"LayerSize": size} for l in range(8)}}
+        else:
+            nd["InitialLayers"] = {}
+        nodes.append(nd)
+    return json.dumps({"Nodes": nodes, "Assignment": {"7": {str(l): {} for l in range(8)}}})
+
+
 CONFIGS = {
+    "refconf": ("the reference's conf/config.json: 8 x 10 930 691 768 B from 7 holders to node 7 (its flow plan: t = 60 s)", reference_conf_json),
     "readme": ("config 1: README JSON, 4 nodes, 1 MiB layers", readme_config),
     "ring64": ("config 2: 8 x 32 x 64 MiB, ring-neighbour partial placement", lambda: stage_config(8, 32, 67_108_864, True)),
     "seed64": ("config 5: 8 x 32 x 64 MiB, one seed GPU", lambda: stage_config(8, 32, 67_108_864, False)),
@@ -54,7 +71,7 @@ CONFIGS = {
 def run(name, desc, text, mode, policy, n_gpu, reps):
     flags = 1 if name == "readme" else 0
     try:
-        plan = d.plan(text, mode, seed=0x5EED, policy=policy, time_scale=1_000_000, flags=flags)
+        plan = d.plan(text, mode, seed=0x5EED, policy=policy, time_scale=1 if name == "refconf" else 1_000_000, flags=flags)
     except d.DissemError as e:
         print(json.dumps({"config": name, "mode": mode, "error": str(e)}), flush=True)
         return
