@@ -65,6 +65,9 @@ def load_library() -> ctypes.CDLL:
         "dissem_host_alloc": (c.c_int, [c.POINTER(P), i64]),
         "dissem_host_free": (c.c_int, [P]),
         "dissem_layer_attach_host": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
+        "dissem_layer_attach_file": (c.c_int, [P, c.c_int, c.c_int, c.c_char_p, i64, i64]),
+        "dissem_layer_detach_file": (c.c_int, [P, c.c_int, c.c_int]),
+        "dissem_layer_file_info": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(i64)]),
         "dissem_layer_export": (c.c_int, [P, c.c_int, c.c_int, P]),
         "dissem_layer_import": (c.c_int, [P, c.c_int, c.c_int, i64, P]),
         "dissem_layer_export_fd": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(c.c_int)]),
@@ -73,6 +76,7 @@ def load_library() -> ctypes.CDLL:
         "dissem_mcast_join": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(c.c_int), c.c_int, c.c_int, c.c_int]),
         "dissem_mcast_bind": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(c.c_int), c.c_int]),
         "dissem_send": (c.c_int, [P, c.c_int, c.c_int, c.c_int, i64, i64, i64, c.POINTER(i64)]),
+        "dissem_send_file": (c.c_int, [P, c.c_int, c.c_int, c.c_int, i64, i64, i64, c.POINTER(i64)]),
         "dissem_schedule_submit": (c.c_int, [P, c.POINTER(Xfer), c.c_int, c.POINTER(i64)]),
         "dissem_schedule_compile": (c.c_int, [P, c.POINTER(Xfer), c.c_int, c.POINTER(i64)]),
         "dissem_schedule_launch": (c.c_int, [P, i64, c.POINTER(i64)]),
@@ -126,6 +130,7 @@ def make_xfers(xfers: Iterable) -> "ctypes.Array[Xfer]":
 
 
 XFER_PULL = 1
+XFER_FILE = 2
 
 
 def plan_directions(xfers: List["Xfer"], gpu_of_node: Sequence[int]) -> List["Xfer"]:
@@ -266,6 +271,18 @@ class Engine:
         """Register pinned, GPU-mapped host memory (dissem_host_alloc) as the node's copy of the layer (source only)."""
         _check(lib().dissem_layer_attach_host(self._ctx, node, layer, ptr, size))
 
+    def attach_file(self, node: int, layer: int, path: str, size: int, file_off: int = 0):
+        """The node holds the layer on disk (DiskLayer): `size` bytes of `path` from `file_off`."""
+        _check(lib().dissem_layer_attach_file(self._ctx, node, layer, path.encode(), file_off, size))
+
+    def detach_file(self, node: int, layer: int):
+        _check(lib().dissem_layer_detach_file(self._ctx, node, layer))
+
+    def file_size(self, node: int, layer: int) -> int:
+        n = ctypes.c_int64()
+        _check(lib().dissem_layer_file_info(self._ctx, node, layer, ctypes.byref(n)))
+        return n.value
+
     def export(self, node: int, layer: int) -> bytes:
         buf = (ctypes.c_uint8 * 64)()
         _check(lib().dissem_layer_export(self._ctx, node, layer, buf))
@@ -302,6 +319,12 @@ class Engine:
     def send(self, src: int, dst: int, layer: int, off: int, size: int, total: int) -> int:
         t = ctypes.c_int64()
         _check(lib().dissem_send(self._ctx, src, dst, layer, off, size, total, ctypes.byref(t)))
+        return t.value
+
+    def send_file(self, src: int, dst: int, layer: int, off: int, size: int, total: int) -> int:
+        """dissem_send from the source node's disk copy; blocks while the file is read."""
+        t = ctypes.c_int64()
+        _check(lib().dissem_send_file(self._ctx, src, dst, layer, off, size, total, ctypes.byref(t)))
         return t.value
 
     def submit(self, xfers) -> int:

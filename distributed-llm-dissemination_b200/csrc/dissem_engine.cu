@@ -1,6 +1,10 @@
 // Host engine behind the C ABI of include/dissem.h: the HBM layer store, the schedule compiler and the
 // launch/wait machinery.  Reference citations are in the header; this file only implements them.
 #include <cuda_runtime.h>
+#include <errno.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <cstdarg>
@@ -58,6 +62,25 @@ unsigned long long *LayerBuf::received() const { return reinterpret_cast<unsigne
 unsigned long long *LayerBuf::csum() const { return reinterpret_cast<unsigned long long *>(base + trailer_off() + 256); }
 int64_t LayerBuf::trailer_bytes() const { return alloc_bytes() - trailer_off(); }
 
+// Disk tier: one staging ring per GPU.  A slot holds one piece of a layer file between pread() and the copy kernel
+// that moves it on; its event tells when that kernel has finished with the slot (and with the slot's descriptor).
+constexpr int kStageSlots = 4;
+constexpr int64_t kStageBytes = 16ll << 20;
+struct StageRing {
+    uint8_t *slot[kStageSlots] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t done[kStageSlots] = {nullptr, nullptr, nullptr, nullptr};
+    bool in_flight[kStageSlots] = {false, false, false, false};
+    XferDesc *d_descs = nullptr;      // one descriptor per slot
+    int next = 0;
+};
+
+// A node's disk copy of a layer (LayerSrc.Fp with Location = DiskLayer, cmd/config.go:147-156)
+struct FileSrc {
+    int fd = -1;
+    int64_t file_off = 0, size = 0;
+    std::string path;
+};
+
 struct DeviceState {
     int dev = -1;
     int n_sm = 0;
@@ -67,6 +90,8 @@ struct DeviceState {
     // cudaMalloc/cudaFree pair per message (cudaFree waits for the whole device).
     XferDesc *desc_pool = nullptr;
     std::vector<int> free_slots;
+    StageRing ring;
+    std::shared_ptr<std::mutex> ring_mu = std::make_shared<std::mutex>();   // one file transfer streams through a ring at a time
 };
 constexpr int kPoolSlots = 256;
 constexpr int kSlotDescs = 16;
@@ -105,6 +130,7 @@ struct dissem_ctx {
     int n_nodes = 0;
     std::vector<int> node_dev_slot;                    // node -> index into devs, or -1 (remote)
     std::vector<std::map<int, LayerBuf>> layers;       // node -> layer -> buffer
+    std::vector<std::map<int, FileSrc>> files;         // node -> layer -> disk copy
     std::vector<DeviceState> devs;
     std::map<int64_t, Sched> scheds;
     std::map<int64_t, Ticket> tickets;
@@ -236,6 +262,10 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
     // Rounds (DISSEM_XFER_ROUND): transfers of round r start after every transfer of round r-1 has completed on every
     // GPU of this process; a relay plan forwards in round r what arrived in round r-1.
     auto round_of = [](const dissem_xfer &x) { return (int)((x.flags >> DISSEM_XFER_ROUND_SHIFT) & 0xFFFF); };
+    for (int i = 0; i < n; ++i)
+        if (xfers[i].flags & DISSEM_XFER_FILE)
+            return set_error(DISSEM_ENOTSUP, "layer %d from node %d's disk copy: a transfer from disk is streamed while its file is read and "
+                             "cannot be compiled; use dissem_schedule_submit or dissem_send_file", xfers[i].layer, xfers[i].src_node);
     std::vector<int> rounds;
     for (int i = 0; i < n; ++i) rounds.push_back(round_of(xfers[i]));
     std::sort(rounds.begin(), rounds.end());
@@ -536,6 +566,136 @@ static void drop_ticket(dissem_ctx *ctx, Ticket &t) {
     t.parts.clear();
 }
 
+// ------------------------------------------------------------------------------------------------
+// disk tier: file -> pinned staging ring -> copy kernel (PCIe in, HBM or NVLink out) with the checksum fused
+// ------------------------------------------------------------------------------------------------
+static int ensure_ring(DeviceState &ds) {
+    StageRing &r = ds.ring;
+    if (r.d_descs) return 0;
+    CUDA_TRY(cudaSetDevice(ds.dev));
+    for (int i = 0; i < kStageSlots; ++i) {
+        // portable + mapped: the kernel of any local GPU dereferences the host pointer itself (unified addressing)
+        if (!r.slot[i]) CUDA_TRY(cudaHostAlloc((void **)&r.slot[i], (size_t)kStageBytes + 256, cudaHostAllocPortable | cudaHostAllocMapped));
+        if (!r.done[i]) CUDA_TRY(cudaEventCreateWithFlags(&r.done[i], cudaEventDisableTiming));
+    }
+    CUDA_TRY(cudaMalloc(&r.d_descs, kStageSlots * sizeof(XferDesc)));
+    return 0;
+}
+
+static int pread_full(const FileSrc &f, uint8_t *dst, int64_t len, int64_t layer_off) {
+    int64_t got = 0;
+    while (got < len) {
+        ssize_t k = pread(f.fd, dst + got, (size_t)(len - got), (off_t)(f.file_off + layer_off + got));
+        if (k < 0 && errno == EINTR) continue;
+        if (k < 0) return set_error(DISSEM_EIO, "reading %s at %lld: %s", f.path.c_str(), (long long)(f.file_off + layer_off + got), strerror(errno));
+        if (k == 0) return set_error(DISSEM_EIO, "%s ends at %lld, before the %lld bytes of the layer", f.path.c_str(),
+                                     (long long)(f.file_off + layer_off + got), (long long)f.size);
+        got += k;
+    }
+    return 0;
+}
+
+// What stream_from_file needs from the store, copied out under ctx->mu so that the file can be read without it.
+struct FileJob {
+    dissem_xfer x;
+    FileSrc file;
+    int dev_slot = -1;
+    uint8_t *dst = nullptr;
+    unsigned long long *csum = nullptr, *received = nullptr;
+    TicketPart tp{-1, nullptr, nullptr, nullptr};
+};
+
+// caller holds ctx->mu
+static int prepare_file_job(dissem_ctx *ctx, const dissem_xfer &x, FileJob *job) {
+    int rc = check_node(ctx, x.src_node);
+    if (rc) return rc;
+    if ((x.flags >> DISSEM_XFER_ROUND_SHIFT) & 0xFFFF)
+        return set_error(DISSEM_ENOTSUP, "layer %d from node %d's disk copy: transfers from disk belong to round 0", x.layer, x.src_node);
+    auto fit = ctx->files[x.src_node].find(x.layer);
+    if (fit == ctx->files[x.src_node].end()) return set_error(DISSEM_ENOENT, "node %d holds no disk copy of layer %d", x.src_node, x.layer);
+    job->x = x;
+    job->file = fit->second;
+    job->dev_slot = ctx->node_dev_slot[x.src_node];              // attach_file accepts local nodes only
+    LayerBuf *dst = nullptr;
+    rc = find_layer(ctx, x.dst_node, x.layer, &dst);
+    if (rc) return rc;
+    if (job->file.size != x.total || dst->size != x.total)
+        return set_error(DISSEM_ERANGE, "layer %d: total %lld but the file holds %lld and dst %lld bytes", x.layer, (long long)x.total,
+                         (long long)job->file.size, (long long)dst->size);
+    if (x.off < 0 || x.size < 0 || x.off + x.size > x.total)
+        return set_error(DISSEM_ERANGE, "layer %d: fragment [%lld,+%lld) outside %lld bytes", x.layer, (long long)x.off, (long long)x.size, (long long)x.total);
+    if (dst->host) return set_error(DISSEM_ENOTSUP, "layer %d: node %d holds it in attached host memory, which can only be a source", x.layer, x.dst_node);
+    job->dst = dst->base;
+    job->csum = dst->csum();
+    job->received = dst->received();
+    DeviceState &ds = ctx->devs[job->dev_slot];
+    CUDA_TRY(cudaSetDevice(ds.dev));
+    job->tp.dev_slot = job->dev_slot;
+    job->tp.start = job->tp.mid = job->tp.end = nullptr;
+    CUDA_TRY(take_event(ctx, ds.dev, &job->tp.start));
+    CUDA_TRY(take_event(ctx, ds.dev, &job->tp.mid));
+    CUDA_TRY(take_event(ctx, ds.dev, &job->tp.end));
+    return 0;
+}
+
+// Runs WITHOUT ctx->mu (other threads keep sending); the ring's own mutex serialises file transfers per GPU.
+// Pieces are cut at multiples of kStageBytes in LAYER space, so a piece covers whole checksum chunks except at the
+// fragment's own two ends; those entries are accumulated into, as for any single-fragment submission.
+static int stream_from_file(dissem_ctx *ctx, FileJob &job, const LaunchCfg &cfg_in, int64_t opt_unit_bytes) {
+    DeviceState &ds = ctx->devs[job.dev_slot];
+    std::lock_guard<std::mutex> ring_lock(*ds.ring_mu);
+    int rc = ensure_ring(ds);
+    if (rc) return rc;
+    StageRing &r = ds.ring;
+    CUDA_TRY(cudaSetDevice(ds.dev));
+    CUDA_TRY(cudaEventRecord(job.tp.start, ds.stream));
+    CUDA_TRY(cudaEventRecord(job.tp.mid, ds.stream));
+    const dissem_xfer &x = job.x;
+    LaunchCfg cfg = cfg_in;
+    cfg.variant = 0;                                   // the source is host memory: register kernel (as for attached host layers)
+    const int64_t end = x.off + x.size;
+    for (int64_t pos = x.off; pos < end;) {
+        const int64_t piece_end = std::min(end, (pos / kStageBytes + 1) * kStageBytes);
+        const int64_t len = piece_end - pos;
+        const int s = r.next;
+        r.next = (r.next + 1) % kStageSlots;
+        if (r.in_flight[s]) {
+            CUDA_TRY(cudaEventSynchronize(r.done[s]));
+            r.in_flight[s] = false;
+        }
+        uint8_t *stage = r.slot[s] + (pos & 255);      // keep the piece's alignment (the kernel vectorises on layer offsets)
+        rc = pread_full(job.file, stage, len, pos);
+        if (rc) return rc;
+        XferDesc d;
+        memset(&d, 0, sizeof d);
+        d.src = reinterpret_cast<const uint8_t *>(reinterpret_cast<uintptr_t>(stage) - (uintptr_t)pos);   // the kernel reads src + layer offset
+        d.dst = job.dst;
+        d.csum = job.csum;
+        d.received = job.received;
+        d.off = pos;
+        d.size = len;
+        d.total = x.total;
+        // units: 256 KiB unless that starves the grid (one piece is at most 64 of them)
+        int shift = kChunkShift;
+        if (opt_unit_bytes > 0) {
+            shift = 12;
+            while ((1ll << shift) < opt_unit_bytes) ++shift;
+            shift = std::min(shift, (int)kChunkShift);
+        } else {
+            while (shift > 14 && units_of(pos, len, shift) < 4ll * ds.n_sm) --shift;
+        }
+        const long long units = units_of(pos, len, shift);
+        CUDA_TRY(cudaMemcpyAsync(r.d_descs + s, &d, sizeof d, cudaMemcpyHostToDevice, ds.stream));   // pageable: staged before return
+        CUDA_TRY(launch_zero_csum(r.d_descs + s, 1, ds.stream));
+        CUDA_TRY(launch_copy_csum(r.d_descs + s, 1, units, shift, ds.counters, cfg, ds.stream, nullptr));
+        CUDA_TRY(cudaEventRecord(r.done[s], ds.stream));
+        r.in_flight[s] = true;
+        pos = piece_end;
+    }
+    CUDA_TRY(cudaEventRecord(job.tp.end, ds.stream));
+    return 0;
+}
+
 }  // namespace dissem
 
 // ====================================================================================================
@@ -568,6 +728,7 @@ int dissem_init(int n_nodes, const int *device_of_node, dissem_ctx **out) {
     ctx->n_nodes = n_nodes;
     ctx->node_dev_slot.assign(n_nodes, -1);
     ctx->layers.resize(n_nodes);
+    ctx->files.resize(n_nodes);
     for (int i = 0; i < n_nodes; ++i) {
         int dev = device_of_node[i];
         if (dev < 0) continue;
@@ -634,8 +795,16 @@ int dissem_close(dissem_ctx *ctx) {
                     cudaFree(lb.base);
                 }
             }
+        for (auto &per_node : ctx->files)
+            for (auto &kv : per_node)
+                if (kv.second.fd >= 0) close(kv.second.fd);
         for (auto &ds : ctx->devs) {
             cudaSetDevice(ds.dev);
+            for (int i = 0; i < kStageSlots; ++i) {
+                if (ds.ring.slot[i]) cudaFreeHost(ds.ring.slot[i]);
+                if (ds.ring.done[i]) cudaEventDestroy(ds.ring.done[i]);
+            }
+            if (ds.ring.d_descs) cudaFree(ds.ring.d_descs);
             cudaFree(ds.counters);
             cudaFree(ds.desc_pool);
             cudaStreamDestroy(ds.stream);
@@ -830,6 +999,61 @@ int dissem_layer_attach_host(dissem_ctx *ctx, int node, int layer, void *pinned,
     lb.device = ds->dev;
     lb.host = true;
     ctx->layers[node][layer] = lb;
+    return DISSEM_OK;
+}
+
+int dissem_layer_attach_file(dissem_ctx *ctx, int node, int layer, const char *path, int64_t file_off, int64_t size) {
+    if (!ctx || !path || file_off < 0 || size < 0) return set_error(DISSEM_EINVAL, "dissem_layer_attach_file: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceState *ds = nullptr;
+    int rc = local_dev(ctx, node, &ds);               // the node's GPU runs the copy kernel that reads the staged pieces
+    if (rc) return rc;
+    if (ctx->files[node].count(layer)) return set_error(DISSEM_EEXIST, "node %d already has a disk copy of layer %d attached", node, layer);
+    FileSrc f;
+    f.fd = open(path, O_RDONLY | O_CLOEXEC);
+    if (f.fd < 0) return set_error(DISSEM_EIO, "open %s: %s", path, strerror(errno));
+    struct stat st;
+    memset(&st, 0, sizeof st);
+    if (fstat(f.fd, &st) != 0 || (int64_t)st.st_size < file_off + size) {
+        const int64_t have = (int64_t)st.st_size;
+        close(f.fd);
+        return set_error(DISSEM_EIO, "%s holds %lld bytes, fewer than offset %lld + layer size %lld", path, (long long)have,
+                         (long long)file_off, (long long)size);
+    }
+    f.file_off = file_off;
+    f.size = size;
+    f.path = path;
+    ctx->files[node][layer] = f;
+    return DISSEM_OK;
+}
+
+int dissem_layer_detach_file(dissem_ctx *ctx, int node, int layer) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    // a transfer that is being streamed holds its ring's mutex, not ctx->mu: wait for those first
+    std::vector<std::shared_ptr<std::mutex>> rings;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        for (auto &ds : ctx->devs) rings.push_back(ds.ring_mu);
+    }
+    for (auto &m : rings) std::lock_guard<std::mutex> wait_for_stream(*m);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = check_node(ctx, node);
+    if (rc) return rc;
+    auto it = ctx->files[node].find(layer);
+    if (it == ctx->files[node].end()) return set_error(DISSEM_ENOENT, "node %d holds no disk copy of layer %d", node, layer);
+    close(it->second.fd);
+    ctx->files[node].erase(it);
+    return DISSEM_OK;
+}
+
+int dissem_layer_file_info(dissem_ctx *ctx, int node, int layer, int64_t *size_out) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = check_node(ctx, node);
+    if (rc) return rc;
+    auto it = ctx->files[node].find(layer);
+    if (it == ctx->files[node].end()) return set_error(DISSEM_ENOENT, "node %d holds no disk copy of layer %d", node, layer);
+    if (size_out) *size_out = it->second.size;
     return DISSEM_OK;
 }
 
@@ -1033,7 +1257,7 @@ int dissem_schedule_info(dissem_ctx *ctx, dissem_sched sched, int64_t *units_out
     return DISSEM_OK;
 }
 
-int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_ticket *out) {
+static int submit_compiled(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_ticket *out) {
     dissem_sched s = 0;
     int rc = dissem_schedule_compile(ctx, xfers, n, &s);
     if (rc) return rc;
@@ -1050,6 +1274,73 @@ int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dis
     return rc;
 }
 
+int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_ticket *out) {
+    if (!ctx || !out || n < 0 || (n > 0 && !xfers)) return set_error(DISSEM_EINVAL, "dissem_schedule_submit: bad arguments");
+    bool any_file = false;
+    for (int i = 0; i < n; ++i) any_file = any_file || (xfers[i].flags & DISSEM_XFER_FILE);
+    if (!any_file) return submit_compiled(ctx, xfers, n, out);
+
+    // Disk tier: the transfers from disk copies are streamed first (this call blocks while their files are read),
+    // the rest of the plan is launched behind them, and one ticket covers both.
+    std::vector<dissem_xfer> rest;
+    std::vector<FileJob> jobs;
+    LaunchCfg cfg{};
+    int64_t unit_bytes = 0;
+    auto give_back = [&](std::vector<FileJob> &js) {                  // caller holds ctx->mu
+        Ticket t;
+        for (auto &j : js)
+            if (j.tp.dev_slot >= 0) t.parts.push_back(j.tp);
+        drop_ticket(ctx, t);
+    };
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        for (int i = 0; i < n; ++i) {
+            if (!(xfers[i].flags & DISSEM_XFER_FILE)) { rest.push_back(xfers[i]); continue; }
+            int rc = check_node(ctx, xfers[i].src_node);
+            if (rc) { give_back(jobs); return rc; }
+            if (ctx->node_dev_slot[xfers[i].src_node] < 0) continue;          // the process that holds the file streams it
+            FileJob job;
+            rc = prepare_file_job(ctx, xfers[i], &job);
+            if (rc) {
+                jobs.push_back(job);
+                give_back(jobs);
+                return rc;
+            }
+            jobs.push_back(job);
+        }
+        cfg = LaunchCfg{0, (int)ctx->opt_ctas_per_sm, 0, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
+        unit_bytes = ctx->opt_unit_bytes;
+    }
+    Ticket ft;
+    int rc = DISSEM_OK;
+    for (auto &job : jobs) {
+        cfg.n_sm = ctx->devs[job.dev_slot].n_sm;
+        rc = stream_from_file(ctx, job, cfg, unit_bytes);
+        if (rc) break;
+    }
+    if (rc == DISSEM_OK && !rest.empty()) rc = submit_compiled(ctx, rest.data(), (int)rest.size(), out);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (rc) {
+        // what was enqueued drains on its own; the events go back once the streams are idle
+        for (auto &ds : ctx->devs) {
+            cudaSetDevice(ds.dev);
+            cudaStreamSynchronize(ds.stream);
+        }
+        give_back(jobs);
+        return rc;
+    }
+    for (auto &job : jobs) ft.parts.push_back(job.tp);
+    if (rest.empty()) {
+        const int64_t id = ctx->next_id++;
+        ctx->tickets[id] = std::move(ft);
+        *out = id;
+    } else {
+        Ticket &t = ctx->tickets[*out];
+        t.parts.insert(t.parts.begin(), ft.parts.begin(), ft.parts.end());
+    }
+    return DISSEM_OK;
+}
+
 int dissem_send(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t off, int64_t size, int64_t total,
                 dissem_ticket *out) {
     dissem_xfer x;
@@ -1057,6 +1348,20 @@ int dissem_send(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t 
     x.src_node = src_node;
     x.dst_node = dst_node;
     x.layer = layer;
+    x.off = off;
+    x.size = size;
+    x.total = total;
+    return dissem_schedule_submit(ctx, &x, 1, out);
+}
+
+int dissem_send_file(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t off, int64_t size, int64_t total,
+                     dissem_ticket *out) {
+    dissem_xfer x;
+    memset(&x, 0, sizeof x);
+    x.src_node = src_node;
+    x.dst_node = dst_node;
+    x.layer = layer;
+    x.flags = DISSEM_XFER_FILE;
     x.off = off;
     x.size = size;
     x.total = total;

@@ -27,6 +27,9 @@ def _bind():
         L.dissem_run_json.argtypes = [c.c_char_p, c.c_int, c.POINTER(c.c_int), c.c_char_p, c.POINTER(c.c_void_p)]
         L.dissem_msg_roundtrip_json.restype = c.c_int
         L.dissem_msg_roundtrip_json.argtypes = [c.c_char_p, c.POINTER(c.c_void_p), c.POINTER(c.c_void_p)]
+        L.dissem_pace_schedule.restype = c.c_int
+        L.dissem_pace_schedule.argtypes = [c.c_int64, c.c_int64, c.c_int64, c.POINTER(c.c_int64), c.POINTER(c.c_int64),
+                                           c.POINTER(c.c_int64), c.c_int, c.POINTER(c.c_int)]
         L.dissem_free.restype = None
         L.dissem_free.argtypes = [c.c_void_p]
         L._host_bound = True
@@ -66,6 +69,20 @@ def run_distribution(config_json: str, mode: int, node_device: Optional[Sequence
     if rc != 0:
         raise HostError(rc, (L.dissem_last_error() or b"").decode())
     return json.loads(_take(L, out))
+
+
+def pace_schedule(layer_off: int, size: int, rate: int):
+    """[(piece_off, piece_size, release_ns)]: when a send limited to `rate` B/s may launch each piece (pure host logic)."""
+    L = _bind()
+    n = ctypes.c_int()
+    rc = L.dissem_pace_schedule(layer_off, size, rate, None, None, None, 0, ctypes.byref(n))
+    if rc != 0:
+        raise HostError(rc, (L.dissem_last_error() or b"").decode())
+    a, b, t = ((ctypes.c_int64 * max(n.value, 1))() for _ in range(3))
+    rc = L.dissem_pace_schedule(layer_off, size, rate, a, b, t, n.value, ctypes.byref(n))
+    if rc != 0:
+        raise HostError(rc, (L.dissem_last_error() or b"").decode())
+    return [(a[i], b[i], t[i]) for i in range(n.value)]
 
 
 def msg_roundtrip(**fields):

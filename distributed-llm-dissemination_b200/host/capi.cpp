@@ -1,4 +1,9 @@
 // C ABI of the host mirror (include/dissem_host.h).
+#include <errno.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
@@ -9,6 +14,7 @@
 #include "config.h"
 #include "message.h"
 #include "node.h"
+#include "pace.h"
 #include "plan.h"
 #include "transport.h"
 
@@ -19,6 +25,46 @@ static char *dup_cstr(const std::string &s) {
     char *p = (char *)malloc(s.size() + 1);
     if (p) memcpy(p, s.c_str(), s.size() + 1);
     return p;
+}
+
+// mkdir -p for the directory part of `path` (os.MkdirAll, cmd/config.go:136)
+static int make_parent_dirs(const std::string &path) {
+    for (size_t i = 1; i < path.size(); ++i)
+        if (path[i] == '/') {
+            const std::string dir = path.substr(0, i);
+            if (mkdir(dir.c_str(), 0755) != 0 && errno != EEXIST) return set_error(DISSEM_EIO, "mkdir %s: %s", dir.c_str(), strerror(errno));
+        }
+    return 0;
+}
+
+// CreateDiskLayer (cmd/config.go:133-157): the file is written only when it does not exist yet.  The reference writes
+// zeros; here the contents follow the run's fill kind, produced by the fill kernel in a scratch HBM buffer of `node`
+// (this library computes nothing on the CPU) and read back.
+static int create_disk_layer(dissem_ctx *ctx, int node, int layer, int64_t size, int fill, uint64_t seed, const std::string &path) {
+    struct stat st;
+    if (stat(path.c_str(), &st) == 0) return 0;
+    int rc = make_parent_dirs(path);
+    if (rc) return rc;
+    rc = dissem_layer_alloc(ctx, node, layer, size);
+    if (rc) return rc;
+    void *host = nullptr;
+    rc = dissem_layer_fill(ctx, node, layer, fill, seed);
+    if (!rc && size > 0) rc = dissem_host_alloc(&host, size);
+    if (!rc && size > 0) rc = dissem_layer_read(ctx, node, layer, host, 0, size);
+    if (!rc) {
+        int fd = open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0644);
+        if (fd < 0) rc = set_error(DISSEM_EIO, "create %s: %s", path.c_str(), strerror(errno));
+        for (int64_t done = 0; !rc && done < size;) {
+            ssize_t k = write(fd, (const char *)host + done, (size_t)(size - done));
+            if (k < 0 && errno == EINTR) continue;
+            if (k <= 0) rc = set_error(DISSEM_EIO, "write %s: %s", path.c_str(), strerror(errno));
+            else done += k;
+        }
+        if (fd >= 0) close(fd);
+    }
+    if (host) dissem_host_free(host);
+    int rc2 = dissem_layer_free(ctx, node, layer);
+    return rc ? rc : rc2;
 }
 
 static PlanOptions make_opts(uint64_t seed, int policy, int64_t time_scale, int flags) {
@@ -200,16 +246,30 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
     if (rc) return rc;
     struct CtxGuard { dissem_ctx *c; ~CtxGuard() { dissem_close(c); } } guard{ctx};
 
-    // CreateLayers for every node, outside the clock as in the reference (cmd/main.go:101 precedes :173)
+    // CreateLayers for every node, outside the clock as in the reference (cmd/main.go:101 precedes :173).
+    // "storage" (the -s flag): the initial layers are files under <storage>/layers/<node>/ instead of HBM buffers.
+    const Json *storage_opt = opts.get("storage");
+    const bool save_disk = storage_opt && storage_opt->kind == Json::String;
+    const std::string storage = save_disk ? storage_opt->s : "";
     for (auto &n : cfg.Nodes)
         for (auto &kv : n.InitialLayers) {
-            rc = dissem_layer_alloc(ctx, (int)n.ID, (int)kv.first, kv.second.LayerSize);
+            const int64_t size = kv.second.LayerSize < 0 ? 0 : kv.second.LayerSize;
+            if (save_disk) {
+                const std::string path = DiskLayerPath(storage, n.ID, kv.first);
+                rc = create_disk_layer(ctx, (int)n.ID, (int)kv.first, size, fill, seed, path);
+                if (rc) return rc;
+                rc = dissem_layer_attach_file(ctx, (int)n.ID, (int)kv.first, path.c_str(), 0, size);
+                if (rc) return rc;
+                continue;
+            }
+            rc = dissem_layer_alloc(ctx, (int)n.ID, (int)kv.first, size);
             if (rc) return rc;
             rc = dissem_layer_fill(ctx, (int)n.ID, (int)kv.first, fill, seed);
             if (rc) return rc;
         }
 
     DeviceFabric fabric(ctx);
+    fabric.pace = opt_i("pace", 0) != 0;
     std::vector<std::unique_ptr<DeviceTransport>> transports;
     std::vector<std::unique_ptr<N>> nodes;
     std::unique_ptr<LeaderNode> leader;
@@ -217,7 +277,7 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
     for (auto &n : cfg.Nodes) {
         transports.emplace_back(new DeviceTransport(&fabric, n.ID));
         nodes.emplace_back(new N(n.ID, leader_conf->ID, transports.back().get()));
-        LayersSrc layers = CreateLayers(n);
+        LayersSrc layers = CreateLayers(n, save_disk, storage);
         if (n.ID == leader_conf->ID) {
             switch (mode) {                                   // RunLeader, cmd/main.go:153-165
                 case 0: leader.reset(new LeaderNode(nodes.back().get(), layers, cfg.Assign)); break;
@@ -281,6 +341,15 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
                 for (auto &x : plan.Xfers)
                     if (x.Dest == na.first && x.Layer == la.first) { received_here = true; src_node = (int)x.Src; }
                 if (!received_here) continue;             // it held the layer from the start
+                if (dissem_layer_info(ctx, src_node, (int)la.first, nullptr, nullptr) == DISSEM_ENOENT &&
+                    dissem_layer_file_info(ctx, src_node, (int)la.first, nullptr) == DISSEM_OK) {
+                    // the source holds the layer on disk only: load it into the source's HBM (outside the clock) to re-read it
+                    dissem_ticket tk = 0;
+                    rc = dissem_layer_alloc(ctx, src_node, (int)la.first, size);
+                    if (!rc) rc = dissem_send_file(ctx, src_node, src_node, (int)la.first, 0, size, size, &tk);
+                    if (!rc) rc = dissem_wait(ctx, tk, nullptr);
+                    if (rc) return rc;
+                }
                 rc = dissem_layer_verify(ctx, src_node, (int)la.first, src_ref.data(), nc);
                 if (rc) return rc;
                 rc = dissem_layer_checksums(ctx, (int)na.first, (int)la.first, fused.data(), nc);
@@ -318,6 +387,19 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
     out.set("xfers", std::move(xs));
     *json_out = dup_cstr(out.dump());
     return *json_out ? DISSEM_OK : set_error(DISSEM_ENOMEM, "out of memory");
+}
+
+int dissem_pace_schedule(int64_t layer_off, int64_t size, int64_t rate_bytes_per_s, int64_t *piece_off, int64_t *piece_size,
+                         int64_t *release_ns, int cap, int *n_out) {
+    if (layer_off < 0 || size < 0 || cap < 0 || !n_out) return set_error(DISSEM_EINVAL, "dissem_pace_schedule: bad arguments");
+    const std::vector<PacePiece> pieces = PaceSchedule(layer_off, size, rate_bytes_per_s);
+    *n_out = (int)pieces.size();
+    for (int i = 0; i < cap && i < (int)pieces.size(); ++i) {
+        if (piece_off) piece_off[i] = pieces[i].off;
+        if (piece_size) piece_size[i] = pieces[i].size;
+        if (release_ns) release_ns[i] = pieces[i].release_ns;
+    }
+    return DISSEM_OK;
 }
 
 }  // extern "C"

@@ -99,14 +99,26 @@ Config ParseConfig(const std::string &text) {
     return cfg;
 }
 
-LayersSrc CreateLayers(const NodeConf &nc) {
+std::string DiskLayerPath(const std::string &storage_path, NodeID node, LayerID layer) {
+    std::string dir = storage_path;
+    if (!dir.empty() && dir.back() != '/') dir += '/';
+    return dir + "layers/" + std::to_string(node) + "/" + std::to_string(layer) + ".layer";
+}
+
+LayersSrc CreateLayers(const NodeConf &nc, bool save_disk, const std::string &storage_path) {
     LayersSrc layers;
     for (auto &kv : nc.InitialLayers) {
         LayerSrc ls;
-        ls.InDevice = true;                                   // CreateInmemLayer, cmd/config.go:159-171
-        ls.DataSize = kv.second.LayerSize;
+        ls.DataSize = kv.second.LayerSize < 0 ? 0 : kv.second.LayerSize;   // cmd/config.go:99-102
         ls.Offset = 0;
-        ls.Meta.Location = InmemLayer;
+        if (save_disk) {                                      // CreateDiskLayer, cmd/config.go:133-157
+            ls.InDevice = false;
+            ls.Fp = DiskLayerPath(storage_path, nc.ID, kv.first);
+            ls.Meta.Location = DiskLayer;
+        } else {                                              // CreateInmemLayer, cmd/config.go:159-171
+            ls.InDevice = true;
+            ls.Meta.Location = InmemLayer;
+        }
         auto it = nc.Sources.find(kv.second.Source);
         ls.Meta.LimitRate = it == nc.Sources.end() ? 0 : it->second;   // cmd/config.go:111
         ls.Meta.DataSize = ls.DataSize;

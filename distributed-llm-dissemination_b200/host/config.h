@@ -39,9 +39,13 @@ struct Config {               // cmd/config.go:14-19
 // ReadJson (cmd/config.go:48-62) — but malformed JSON is an error here, not silently ignored (:59).
 Config ParseConfig(const std::string &text);
 
-// CreateLayers (cmd/config.go:94-117): the LayersSrc a node starts with.  All layers are in device memory
-// (no -s path on the GPU box); Meta.LimitRate = Sources[sourceType] (:111).
-LayersSrc CreateLayers(const NodeConf &nc);
+// CreateLayers (cmd/config.go:94-117): the LayersSrc a node starts with; Meta.LimitRate = Sources[sourceType] (:111).
+// save_disk (the `-s` flag, :105-106): the layers are files `<storage_path>/layers/<node id>/<layer id>.layer`
+// (CreateDiskLayer, :133-157) with Location = DiskLayer; otherwise they are in device memory (CreateInmemLayer).
+// Only the descriptions are made here; the caller creates the files / HBM buffers.
+LayersSrc CreateLayers(const NodeConf &nc, bool save_disk = false, const std::string &storage_path = "");
+// The path CreateDiskLayer gives a layer file (cmd/config.go:135-139).
+std::string DiskLayerPath(const std::string &storage_path, NodeID node, LayerID layer);
 
 }  // namespace host
 }  // namespace dissem

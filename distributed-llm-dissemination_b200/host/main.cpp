@@ -11,20 +11,22 @@
 #include "../../include/dissem_host.h"
 
 int main(int argc, char **argv) {
-    int id = -1, mode = -1, verbose = 0, batched = 0, gpus = 1;
+    int id = -1, mode = -1, verbose = 0, batched = 0, gpus = 1, pace = 0;
     std::string file, storage;
+    bool save_disk = false;
     long long time_scale = 1000000;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         auto next = [&]() -> const char * { return i + 1 < argc ? argv[++i] : ""; };
         if (a == "-id") id = atoi(next());
         else if (a == "-f") file = next();
-        else if (a == "-s") storage = next();
+        else if (a == "-s") { storage = next(); save_disk = !storage.empty(); }   // cmd/main.go:93-96: layers live in files under this path
         else if (a == "-m") mode = atoi(next());
         else if (a == "-l") { printf("layer set up\n"); return 0; }   // cmd/main.go:108-111: layers are synthesised in HBM at start
         else if (a == "-c") { fprintf(stderr, "external clients are outside the device transport's scope\n"); return 2; }
         else if (a == "-v") verbose = 1;
         else if (a == "--batched") batched = 1;
+        else if (a == "--pace") pace = 1;                             // honour LimitRate as writeWithLimit does (transport.go:407-424)
         else if (a == "--gpus") gpus = atoi(next());
         else if (a == "--time-scale") time_scale = atoll(next());
     }
@@ -41,11 +43,17 @@ int main(int argc, char **argv) {
     if (gpus > n_dev) gpus = n_dev;
     int devs[4096];
     for (int i = 0; i < 4096; ++i) devs[i] = i % gpus;
-    char opts[256];
-    snprintf(opts, sizeof opts, "{\"batched\":%d,\"time_scale\":%lld,\"flags\":3,\"seed\":24301}", batched, time_scale);
+    std::string opts = "{\"batched\":" + std::to_string(batched) + ",\"time_scale\":" + std::to_string(time_scale) +
+                       ",\"flags\":3,\"seed\":24301,\"pace\":" + std::to_string(pace);
+    if (save_disk) {
+        std::string esc;
+        for (char ch : storage) { if (ch == '"' || ch == '\\') esc += '\\'; esc += ch; }
+        opts += ",\"storage\":\"" + esc + "\"";
+    }
+    opts += "}";
     printf("launching leader...\n[id: %d, filename: %s, storagePath: %s, mode: %d]\n", id, file.c_str(), storage.c_str(), mode);
     char *out = nullptr;
-    int rc = dissem_run_json(ss.str().c_str(), mode, devs, opts, &out);
+    int rc = dissem_run_json(ss.str().c_str(), mode, devs, opts.c_str(), &out);
     if (rc) { fprintf(stderr, "leader failed: %s\n", dissem_last_error()); return 1; }
     // pull time_to_deliver_ms out of the report
     const char *p = strstr(out, "\"time_to_deliver_ms\":");

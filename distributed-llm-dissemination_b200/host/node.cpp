@@ -93,7 +93,12 @@ void RoleBase::StoreLayer(const LayerMsg &m, bool *complete) {
         it = layers_.emplace(m.Layer, ls).first;
     }
     LayerSrc &ls = it->second;
+    if (ls.Meta.Location == DiskLayer) {       // the delivery replaces a disk copy with the in-memory one (node.go:1372)
+        ls.DataSize = 0;
+        ls.Fp.clear();
+    }
     if (ls.DataSize < m.TotalSize) ls.DataSize += m.Src_.DataSize;       // node.go:1540-1543
+    ls.InDevice = true;
     ls.Meta.Location = InmemLayer;
     ls.Meta.DataSize = m.TotalSize;
     *complete = ls.DataSize == m.TotalSize;                              // node.go:1555
@@ -665,9 +670,10 @@ int HandleFlowRetransmit(N *node, const LayersSrc &layers, const FlowRetransmitM
     lm->Layer = m.Layer;
     lm->Src_ = partial;
     lm->TotalSize = total;
-    if (m.DestID == node->GetMyID()) {
+    if (m.DestID == node->GetMyID() && partial.Meta.Location != DiskLayer) {
         // self job: the destination already holds the layer; the reference ships it to itself over TCP
-        // (node.go:1239-1248); here only the header is delivered so that the ack still flows.
+        // (node.go:1239-1248); here only the header is delivered so that the ack still flows.  A layer held on DISK
+        // does take the transport: the send to itself is what loads the file into the node's HBM.
         node->GetTransport()->Deliver().Push(DecodeMsg(EncodeMsg(*lm)));
         return 0;
     }

@@ -71,9 +71,14 @@ Plan PlanMode1(NodeID leader, const LayersSrc &leader_layers, const Status &stat
             if (ow == owners.end() || ow->second.empty())
                 throw PlanError("mode 1: nobody holds layer " + std::to_string(la.first));
             const std::vector<NodeID> &own = ow->second;
-            if (std::find(own.begin(), own.end(), na.first) != own.end()) continue;          // node.go:578-580
             NodeID owner;
-            if (opt.Policy == OwnerRandom) {
+            if (std::find(own.begin(), own.end(), na.first) != own.end()) {
+                // node.go:578-580 skips a destination that announced the layer, wherever it keeps it; a copy on DISK then
+                // never reaches memory and assignmentSatisfied (node.go:440) never holds: the reference waits forever.
+                // Fixed here: such a node is told to send the layer to itself, which loads the file into its HBM.
+                if (status.at(na.first).at(la.first).Location == InmemLayer) continue;
+                owner = na.first;
+            } else if (opt.Policy == OwnerRandom) {
                 uint64_t h = Mix64(opt.Seed + (uint64_t)(na.first + 1) * 0x9E3779B97F4A7C15ull +
                                    (uint64_t)(la.first + 1) * 0xD1B54A32D192ED03ull);
                 owner = own[h % own.size()];
@@ -145,7 +150,9 @@ Plan PlanMode3(NodeID leader, const LayersSrc &leader_layers, const Status &stat
         x.Offset = j.Offset;
         x.DataSize = j.DataSize;
         x.TotalSize = sizes[j.Layer];
-        x.Rate = p.MinTime > 0 ? j.DataSize / p.MinTime : 0;    // node.go:1281
+        // node.go:1281: rate = dataSize / minTime, bytes per second.  With a finer clock (TimeScale ticks per second)
+        // minTime is in ticks, so the same quotient is scaled back to bytes per second.
+        x.Rate = p.MinTime > 0 ? (int64_t)std::min<__int128>((__int128)j.DataSize * opt.Flow.TimeScale / p.MinTime, INT64_MAX) : 0;
         p.Xfers.push_back(x);
     }
     return p;

@@ -1,9 +1,12 @@
 #include "transport.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
+#include <thread>
 
 #include "../csrc/dissem_engine.h"
+#include "pace.h"
 
 namespace dissem {
 namespace host {
@@ -90,23 +93,57 @@ int DeviceTransport::Send(NodeID dest, MessagePtr message) {
     DeviceTransport *peer = fabric_->Lookup(dest);
     if (!peer) return set_error(DISSEM_ENOENT, "addr of %u does not exist", dest);     // transport.go:263-265
     if (auto *lm = dynamic_cast<LayerMsg *>(message.get())) {
-        if (!lm->Src_.InDevice || lm->Src_.Meta.Location != InmemLayer)
-            return set_error(DISSEM_EINVAL, "unknown error sending layer %u", lm->Layer);   // transport.go:368-370
+        const bool in_device = lm->Src_.InDevice && lm->Src_.Meta.Location == InmemLayer;      // transport.go:333
+        const bool on_disk = lm->Src_.Meta.Location == DiskLayer;                              // transport.go:351
+        if (!in_device && !on_disk) return set_error(DISSEM_EINVAL, "unknown error sending layer %u", lm->Layer);   // transport.go:368-370
+        if (on_disk && lm->Src_.Fp.empty()) return set_error(DISSEM_EINVAL, "no data source specified");         // transport.go:352-354
         int rc = EnsureDestLayer(dest, lm->Layer, lm->TotalSize);
         if (rc) return rc;
         dissem_ticket ticket = 0;
-        rc = dissem_send(fabric_->ctx(), (int)lm->SrcID, (int)dest, (int)lm->Layer, lm->Src_.Offset, lm->Src_.DataSize,
-                         lm->TotalSize, &ticket);
+        if (on_disk) {
+            // the section reader over the layer file (transport.go:356-364): the engine streams the file through pinned
+            // staging buffers into the destination.  The file was attached when the node's layers were created.
+            rc = dissem_send_file(fabric_->ctx(), (int)lm->SrcID, (int)dest, (int)lm->Layer, lm->Src_.Offset, lm->Src_.DataSize,
+                                  lm->TotalSize, &ticket);
+        } else if (fabric_->pace && lm->Src_.Meta.LimitRate > 0) {
+            // writeWithLimit (transport.go:407-424): pieces are launched no earlier than the reference's token bucket
+            // would have let their last byte go; the file branch above is not limited in the reference either (:364)
+            const auto t0 = std::chrono::steady_clock::now();
+            std::vector<dissem_ticket> in_flight;
+            for (const PacePiece &pc : PaceSchedule(lm->Src_.Offset, lm->Src_.DataSize, lm->Src_.Meta.LimitRate)) {
+                std::this_thread::sleep_until(t0 + std::chrono::nanoseconds(pc.release_ns));
+                dissem_ticket tk = 0;
+                rc = dissem_send(fabric_->ctx(), (int)lm->SrcID, (int)dest, (int)lm->Layer, pc.off, pc.size, lm->TotalSize, &tk);
+                if (rc) break;
+                in_flight.push_back(tk);
+            }
+            double paced_ms = 0.0;
+            for (dissem_ticket tk : in_flight) {                 // every ticket is waited for, also after an error
+                double one = 0.0;
+                int rcw = dissem_wait(fabric_->ctx(), tk, &one);
+                if (!rc) rc = rcw;
+                paced_ms += one;
+            }
+            if (rc) return rc;
+            {
+                std::lock_guard<std::mutex> lk(fabric_->stat_mu);
+                fabric_->device_ms += paced_ms;
+                fabric_->launches += 2 * (int64_t)in_flight.size();
+            }
+        } else {
+            rc = dissem_send(fabric_->ctx(), (int)lm->SrcID, (int)dest, (int)lm->Layer, lm->Src_.Offset, lm->Src_.DataSize,
+                             lm->TotalSize, &ticket);
+        }
         if (rc) return rc;
         double ms = 0.0;
-        rc = dissem_wait(fabric_->ctx(), ticket, &ms);          // Send returns when the bytes are written
+        if (ticket) rc = dissem_wait(fabric_->ctx(), ticket, &ms);          // Send returns when the bytes are written
         if (rc) return rc;
         {
             std::lock_guard<std::mutex> lk(fabric_->stat_mu);
             fabric_->layer_msgs++;
             fabric_->layer_bytes += lm->Src_.DataSize;
             fabric_->device_ms += ms;
-            fabric_->launches += lm->Src_.DataSize > 0 ? 2 : 0;
+            fabric_->launches += (ticket && lm->Src_.DataSize > 0) ? 2 : 0;
         }
         // what handleIncomingMsg hands to the node (transport.go:221-222): header fields + an in-memory LayerSrc
         auto delivered = std::dynamic_pointer_cast<LayerMsg>(DecodeMsg(EncodeMsg(*lm)));
@@ -123,6 +160,12 @@ int DeviceTransport::Send(NodeID dest, MessagePtr message) {
 
 int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *device_ms_out) {
     std::vector<dissem_xfer> xs;
+    bool any_file = false;
+    // which sources are disk copies is settled before any destination buffer is created (a node may load its own file)
+    std::vector<int> from_file;
+    for (auto &x : xfers)
+        from_file.push_back(dissem_layer_info(fabric_->ctx(), (int)x.Src, (int)x.Layer, nullptr, nullptr) == DISSEM_ENOENT &&
+                            dissem_layer_file_info(fabric_->ctx(), (int)x.Src, (int)x.Layer, nullptr) == DISSEM_OK);
     for (auto &x : xfers) {
         int rc = EnsureDestLayer(x.Dest, x.Layer, x.TotalSize);
         if (rc) return rc;
@@ -130,7 +173,12 @@ int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *de
         d.src_node = (int32_t)x.Src;
         d.dst_node = (int32_t)x.Dest;
         d.layer = (int32_t)x.Layer;
+        // a source that holds the layer on disk only (DiskLayer) is read from its file
         d.flags = 0;
+        if (from_file[xs.size()]) {
+            d.flags = DISSEM_XFER_FILE;
+            any_file = true;
+        }
         d.off = x.Offset;
         d.size = x.DataSize;
         d.total = x.TotalSize;
@@ -146,11 +194,17 @@ int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *de
     }
     dissem_xfer *opt = nullptr;
     int n_opt = 0;
-    int rc = dissem_plan_optimize(xs.data(), (int)xs.size(), gpu_of_node.data(), n_nodes, &opt, &n_opt, nullptr);
-    if (rc) return rc;
+    int rc = 0;
     dissem_ticket ticket = 0;
-    rc = dissem_schedule_submit(fabric_->ctx(), opt, n_opt, &ticket);
-    free(opt);
+    if (any_file) {
+        // relay chains and pulls assume HBM-resident sources: a plan with disk sources is submitted as planned
+        rc = dissem_schedule_submit(fabric_->ctx(), xs.data(), (int)xs.size(), &ticket);
+    } else {
+        rc = dissem_plan_optimize(xs.data(), (int)xs.size(), gpu_of_node.data(), n_nodes, &opt, &n_opt, nullptr);
+        if (rc) return rc;
+        rc = dissem_schedule_submit(fabric_->ctx(), opt, n_opt, &ticket);
+        free(opt);
+    }
     if (rc) return rc;
     double ms = 0.0;
     rc = dissem_wait(fabric_->ctx(), ticket, &ms);

@@ -55,6 +55,9 @@ public:
     void Unregister(NodeID id);
     DeviceTransport *Lookup(NodeID id);
     std::vector<NodeID> Ids();
+    // LimitRate pacing (pace.h): off by default — NVLink is not the network the reference throttles for; switched on
+    // to reproduce the reference's timing behaviour (`"pace":1` / --pace).
+    bool pace = false;
     // counters for the run report
     std::mutex stat_mu;
     int64_t layer_msgs = 0, layer_bytes = 0, control_msgs = 0, launches = 0;

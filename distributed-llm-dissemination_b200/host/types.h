@@ -34,7 +34,7 @@ using NodeIDs = std::set<NodeID>;                       // node.go:132
 // (node, layer); the fields the reference uses for slicing a fragment are kept.
 struct LayerSrc {
     bool InDevice = false;   // stands for InmemData != nil
-    std::string Fp;          // unused (no disk tier on the GPU path)
+    std::string Fp;          // DiskLayer: the layer file, attached to the engine with dissem_layer_attach_file
     int64_t DataSize = 0;
     int64_t Offset = 0;
     LayerMeta Meta;

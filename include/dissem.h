@@ -45,6 +45,7 @@ extern "C" {
 #define DISSEM_ENOTSUP -8  /* capability missing on this box (e.g. NVLS multicast) */
 #define DISSEM_EPARSE -9   /* malformed config JSON */
 #define DISSEM_EPLAN -10   /* the mode cannot serve this placement (e.g. mode 0, leader lacks a layer) */
+#define DISSEM_EIO -11     /* a layer file could not be opened or read (disk tier) */
 
 typedef struct dissem_ctx dissem_ctx;
 typedef int64_t dissem_ticket;   /* one submitted batch of transfers */
@@ -57,6 +58,9 @@ typedef int64_t dissem_sched;    /* one compiled schedule */
 /* dissem_xfer.flags: who executes the transfer.  Default (0): the GPU holding the source pushes.  PULL: the
  * destination's GPU loads from the source instead (its process needs the source layer imported). */
 #define DISSEM_XFER_PULL 1
+/* FILE: the source is src_node's DISK copy of the layer (dissem_layer_attach_file; LayerSrc with Location = DiskLayer,
+ * transport.go:351-367), not its HBM copy.  Such transfers are streamed by dissem_schedule_submit / dissem_send_file. */
+#define DISSEM_XFER_FILE 2
 /* Bits 8..23 of flags: the transfer's ROUND.  Within one dissem_schedule_* call the transfers of round r start
  * only after every transfer of round r-1 has completed on every GPU of this process (device-side event waits, no
  * host round trip).  A relay plan (dissem_plan_relay) forwards in round r the piece that arrived in round r-1.
@@ -113,6 +117,19 @@ int dissem_host_free(void *p);
  * their source are read by the copy kernel straight over PCIe, so upload and dissemination are one pass.  Such a
  * copy can only be a source: it has no checksum table or received counter and cannot be exported. */
 int dissem_layer_attach_host(dissem_ctx *ctx, int node, int layer, void *pinned, int64_t size);
+/* The disk tier (DiskLayer / `-s`, cmd/config.go:133-157; sent with a section reader over the file,
+ * transport.go:351-367).  Records that `node` holds `layer` as `size` bytes of the file `path` starting
+ * at `file_off`.  The file is opened read-only and stays open until dissem_layer_detach_file / dissem_close; nothing is
+ * read here.  This is independent of the node's HBM copy (dissem_layer_alloc), which may or may not exist: a transfer
+ * names the disk copy with DISSEM_XFER_FILE, exactly as a layerMsg carries its LayerSrc.Meta.Location.  A transfer from
+ * the disk copy is staged through a ring of pinned host buffers (4 x 16 MiB per GPU, allocated on first use): the
+ * calling thread reads the next piece of the file while the copy kernel of the node's GPU moves the previous pieces
+ * over PCIe into the destination and folds them into its checksum table.  The node may be its own destination
+ * (loading its disk copy into HBM). */
+int dissem_layer_attach_file(dissem_ctx *ctx, int node, int layer, const char *path, int64_t file_off, int64_t size);
+int dissem_layer_detach_file(dissem_ctx *ctx, int node, int layer);
+/* size_out: the attached size; DISSEM_ENOENT when the node has no disk copy of the layer. */
+int dissem_layer_file_info(dissem_ctx *ctx, int node, int layer, int64_t *size_out);
 
 /* ---- one process per GPU: make a local layer reachable from peer processes -------------------------- */
 /* handle_out: 64 opaque bytes to ship over the control plane (e.g. inside the announceMsg, message.go:31-41). */
@@ -142,6 +159,13 @@ int dissem_mcast_bind(dissem_ctx *ctx, int layer, int src_node, const int *dst_n
  * local to this process are executed; others are skipped (their owner process runs them). */
 int dissem_send(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t off, int64_t size,
                 int64_t total, dissem_ticket *out);
+/* The same from src_node's disk copy (DISSEM_XFER_FILE).  Returns once the last piece of the file has been read and
+ * its copy enqueued (sendLayerMsg blocks in io.Copy likewise, transport.go:364); the ticket completes when the bytes
+ * have landed.  Transfers from disk cannot be part of a compiled schedule (dissem_schedule_compile: DISSEM_ENOTSUP)
+ * or of a round other than 0; in dissem_schedule_submit they are streamed first, one after another, and the rest of
+ * the plan is launched behind them. */
+int dissem_send_file(dissem_ctx *ctx, int src_node, int dst_node, int layer, int64_t off, int64_t size,
+                     int64_t total, dissem_ticket *out);
 /* A whole plan at once (what LeaderNode.sendLayers / RetransmitLeaderNode.sendLayers / dispatchJob issue
  * one goroutine at a time, node.go:326-352, :554-626, :1237-1288): compiled into one launch per source
  * GPU.  dissem_schedule_submit = compile + launch + free. */

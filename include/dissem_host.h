@@ -43,9 +43,14 @@ void dissem_free(void *p);
  * leader and receivers as threads speaking the reference's control-plane messages (message.go) over an
  * in-process Transport whose layer branch is the device engine.  Needs a GPU.
  * node_device[i]: CUDA ordinal for the config's i-th node (NULL = all on device 0).
- * opts_json (may be NULL): {"seed":S,"policy":P,"time_scale":T,"flags":F,"fill":K,"batched":bool,"verify":bool}
+ * opts_json (may be NULL): {"seed":S,"policy":P,"time_scale":T,"flags":F,"fill":K,"batched":bool,"verify":bool,
+ *                           "storage":"<path>","pace":bool}
  *   batched=false: one Transport.Send per layerMsg, as the reference issues them;
- *   batched=true : the leader hands the whole plan to dissem_schedule_submit (one launch per source GPU).
+ *   batched=true : the leader hands the whole plan to dissem_schedule_submit (one launch per source GPU);
+ *   storage      : the `-s` flag (cmd/main.go:17, :93-101): every node's initial layers are files
+ *                  <path>/layers/<node id>/<layer id>.layer (CreateDiskLayer, cmd/config.go:133-157; written when missing,
+ *                  with the run's fill) attached with dissem_layer_attach_file and sent as DiskLayer sources;
+ *   pace         : unbatched layer sends honour LayerSrc.Meta.LimitRate as writeWithLimit does (dissem_pace_schedule).
  * *json_out: {"time_to_deliver_ms":..,"device_ms":..,"bytes":..,"n_xfers":..,"acks":..,"verified":bool,...} */
 int dissem_run_json(const char *config_json, int mode, const int *node_device, const char *opts_json,
                     char **json_out);
@@ -54,6 +59,16 @@ int dissem_run_json(const char *config_json, int mode, const int *node_device, c
  * envelope {"type":T,"src":"<id>","payload":{...}} and decode it back; used by the parity tests.
  * kind_json: {"kind":"announce|ack|retransmit|flowRetransmit|startup|simple|layerHeader", fields...}. */
 int dissem_msg_roundtrip_json(const char *kind_json, char **wire_out, char **decoded_out);
+
+/* LimitRate pacing: TcpTransport.writeWithLimit (transport.go:407-424) sends a fragment in sub-writes of at most
+ * 256 KiB, each after rate.Limiter.WaitN (golang.org/x/time/rate v0.14.0, go.mod:8; burst = 256 KiB, bucket full at
+ * the start).  This returns the device-side schedule for the `size` bytes at `layer_off` of a layer: pieces that end on
+ * 256 KiB boundaries of the layer, each with the earliest time (ns after the send began) at which the reference's
+ * limiter would have released the sub-write holding the piece's last byte; the last piece is released when the
+ * reference's last sub-write is.  rate <= 0 means unlimited (one piece at 0; the reference's limiter would never
+ * finish).  Fills at most `cap` entries of each non-NULL array; *n_out = the number of pieces.  Pure host arithmetic. */
+int dissem_pace_schedule(int64_t layer_off, int64_t size, int64_t rate_bytes_per_s, int64_t *piece_off,
+                         int64_t *piece_size, int64_t *release_ns, int cap, int *n_out);
 
 #ifdef __cplusplus
 }

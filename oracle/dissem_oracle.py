@@ -594,6 +594,70 @@ def apply_transfers(store: Dict[Tuple[int, int], np.ndarray], xfers: Iterable[Xf
     return store
 
 
+# --------------------------------------------------------------------------------------
+# disk tier (`-s`): layers kept as files
+# --------------------------------------------------------------------------------------
+def disk_layer_path(storage_path: str, node: int, layer: int) -> str:
+    """CreateDiskLayer's file name, cmd/config.go:135-139: <storage>/layers/<node id>/<layer id>.layer"""
+    import os
+    return os.path.join(storage_path, "layers", str(node), f"{layer}.layer")
+
+
+def create_disk_layer(storage_path: str, node: int, layer: int, size: int, contents: Optional[np.ndarray] = None) -> str:
+    """CreateDiskLayer, cmd/config.go:133-157: make the directory, write the file only if it does not exist yet.
+    The reference writes `size` zero bytes (:141-142); `contents` lets a test put recognisable bytes there instead."""
+    import os
+    path = disk_layer_path(storage_path, node, layer)
+    os.makedirs(os.path.dirname(path), mode=0o755, exist_ok=True)
+    if not os.path.exists(path):
+        data = np.zeros(max(size, 0), dtype=np.uint8) if contents is None else np.ascontiguousarray(contents, dtype=np.uint8)
+        with open(path, "wb") as f:
+            f.write(data.tobytes())
+    return path
+
+
+def read_disk_section(path: str, off: int, size: int) -> np.ndarray:
+    """What sendLayerMsg puts on the wire for a DiskLayer (transport.go:356-364): the section
+    [Offset, Offset+DataSize) of the file, through io.NewSectionReader + io.Copy."""
+    with open(path, "rb") as f:
+        f.seek(off)
+        data = f.read(size)
+    return np.frombuffer(data, dtype=np.uint8).copy()
+
+
+# --------------------------------------------------------------------------------------
+# LimitRate pacing: golang.org/x/time/rate v0.14.0 (go.mod:8; not under /root/reference) as
+# writeWithLimit drives it (transport.go:407-424).  PARITY UNPINNED: no reference test exercises it.
+# --------------------------------------------------------------------------------------
+PACE_BURST = 256 * 1024            # BucketSize, transport.go:408
+
+
+def limiter_write_times(size: int, rate: int, burst: int = PACE_BURST) -> List[Tuple[int, int, int]]:
+    """[(release_ns, cumulative_start, n)] for every conn.Write of writeWithLimit(limitRate=rate, data of `size` bytes):
+    n = min(len(data), burst); limiter.WaitN(ctx, n); write.  The limiter is the published token bucket:
+    NewLimiter starts with `burst` tokens; reserveN advances tokens by elapsed*limit capped at burst, subtracts n, and
+    a negative balance waits -tokens/limit seconds (truncated to whole ns, as time.Duration is).  Virtual time: a
+    write takes no time, the next WaitN is called when the previous one returns."""
+    if rate <= 0:
+        raise ValueError("rate.Limit(0) never grants a second write: the reference hangs (SURVEY fact 9)")
+    out = []
+    tokens = float(burst)
+    last = 0            # ns, lim.last
+    now = 0
+    pos = 0
+    while pos < size:
+        n = min(size - pos, burst)
+        elapsed = max(0, now - last)
+        tokens = min(float(burst), tokens + (elapsed / 1e9) * float(rate))      # advance()
+        tokens -= float(n)
+        wait = int(1e9 * (-tokens / float(rate))) if tokens < 0 else 0           # durationFromTokens
+        last = now
+        now = now + wait                                                         # WaitN sleeps until timeToAct
+        out.append((now, pos, n))
+        pos += n
+    return out
+
+
 def assignment_satisfied(cfg: Config, store: Dict[Tuple[int, int], np.ndarray]) -> bool:
     """assignmentSatisfied, node.go:435-446 (presence in memory; content is ours to add)."""
     return all((n, l) in store for n, ls in cfg.assignment.items() for l in ls)

@@ -313,3 +313,42 @@ def test_plan_digests_are_stable():
                 assert got == want, key
                 seen += 1
     assert seen >= 30 and len(gold) == 40
+
+
+@pytest.mark.parametrize("off,size,rate", [
+    (0, 1, 1000), (0, 262144, 1 << 20), (0, 262145, 1 << 20), (0, 5 * 262144 + 100, 20_000_000),
+    (13, 3 * 262144, 7_000_000), (262144 - 1, 2, 1 << 20), (5 * 262144 + 77, 40 * 262144 + 5, 3_000_000_000),
+    (100_003, 64 << 20, 200_000_000_000), (0, 1 << 30, 900_000_000_000),
+])
+def test_pace_schedule_never_runs_ahead_of_the_reference_limiter(off, size, rate):
+    """writeWithLimit (transport.go:407-424) over x/time/rate's token bucket, restated in the oracle: a piece is released
+    no earlier than the sub-write that carries its last byte, and the last piece exactly when the last sub-write is."""
+    pieces = host.pace_schedule(off, size, rate)
+    writes = o.limiter_write_times(size, rate)
+    assert pieces[0][0] == off and sum(p[1] for p in pieces) == size
+    for (a, n, _), (b, _, _) in zip(pieces[:-1], pieces[1:]):
+        assert a + n == b and b % 262144 == 0                   # pieces tile the fragment and end on checksum chunks
+    tol = len(writes) + 2                                       # the limiter truncates every wait to whole ns
+    starts = [w[1] for w in writes]
+    import bisect
+    for (a, n, t_ns) in pieces:
+        last_byte = a + n - 1 - off
+        w = writes[bisect.bisect_right(starts, last_byte) - 1]
+        assert w[1] <= last_byte < w[1] + w[2]
+        assert abs(t_ns - w[0]) <= tol, (a, n, t_ns, w)
+    assert abs(pieces[-1][2] - writes[-1][0]) <= tol
+    assert all(x[2] <= y[2] for x, y in zip(pieces[:-1], pieces[1:]))
+    # launches are spaced: at most ~4000 a second unless the reference's own 256 KiB quantum is coarser
+    if len(pieces) > 2:
+        gaps = [y[2] - x[2] for x, y in zip(pieces[1:-2], pieces[2:-1])]
+        assert all(g >= min(240_000, int(262144 / rate * 1e9) - 1) for g in gaps)
+
+
+def test_pace_schedule_edge_cases():
+    assert host.pace_schedule(0, 0, 1000) == []
+    assert host.pace_schedule(7, 1 << 20, 0) == [(7, 1 << 20, 0)]          # 0 = unlimited here (the reference would hang)
+    assert host.pace_schedule(7, 1 << 20, -5) == [(7, 1 << 20, 0)]
+    with pytest.raises(host.HostError):
+        host.pace_schedule(-1, 10, 10)
+    with pytest.raises(ValueError):
+        o.limiter_write_times(10, 0)

@@ -188,3 +188,18 @@ def test_tcp_baseline_delivers_bytes():
     frs = [o.Xfer(0, 1, 2, 0, 100_001, 300_000), o.Xfer(0, 1, 2, 100_001, 199_999, 300_000)]
     sec, moved = co.tcp_run(4, 0, frs, [layers[2], layers[2]], base_port=19180, verify=True)
     assert moved == 300_000
+
+
+def test_disk_layer_restatement(tmp_path):
+    """CreateDiskLayer (cmd/config.go:133-157): <storage>/layers/<node>/<layer>.layer, zeros, written only when missing;
+    a DiskLayer goes on the wire as the file section [Offset, Offset+DataSize) (transport.go:356-364)."""
+    p = o.create_disk_layer(str(tmp_path), 3, 11, 5000)
+    assert p == str(tmp_path / "layers" / "3" / "11.layer")
+    assert not o.read_disk_section(p, 0, 5000).any()
+    marked = o.fill_bytes(o.FILL_PATTERN, 11, 5000, 7)
+    with open(p, "r+b") as f:
+        f.write(marked.tobytes())
+    assert o.create_disk_layer(str(tmp_path), 3, 11, 5000) == p            # exists: left as it is
+    assert np.array_equal(o.read_disk_section(p, 0, 5000), marked)
+    assert np.array_equal(o.read_disk_section(p, 123, 1000), marked[123:1123])
+    assert o.create_disk_layer(str(tmp_path), 3, 12, -4) and o.read_disk_section(o.disk_layer_path(str(tmp_path), 3, 12), 0, 10).size == 0
