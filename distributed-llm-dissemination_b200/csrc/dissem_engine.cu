@@ -15,6 +15,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/dissem.h"
@@ -141,7 +142,7 @@ struct dissem_ctx {
     std::string mcast_note;
     std::vector<cudaEvent_t> event_pool[64];   // per device ordinal: events are reused across launches
     // options
-    int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0, opt_alloc_vmm = 0, opt_mcast = 1;
+    int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0, opt_alloc_vmm = 0, opt_mcast = 1, opt_file_threads = 8;
 };
 
 namespace dissem {
@@ -582,16 +583,49 @@ static int ensure_ring(DeviceState &ds) {
     return 0;
 }
 
-static int pread_full(const FileSrc &f, uint8_t *dst, int64_t len, int64_t layer_off) {
+static int pread_range(const FileSrc &f, uint8_t *dst, int64_t len, int64_t layer_off, std::string *err) {
     int64_t got = 0;
+    char buf[512];
     while (got < len) {
         ssize_t k = pread(f.fd, dst + got, (size_t)(len - got), (off_t)(f.file_off + layer_off + got));
         if (k < 0 && errno == EINTR) continue;
-        if (k < 0) return set_error(DISSEM_EIO, "reading %s at %lld: %s", f.path.c_str(), (long long)(f.file_off + layer_off + got), strerror(errno));
-        if (k == 0) return set_error(DISSEM_EIO, "%s ends at %lld, before the %lld bytes of the layer", f.path.c_str(),
-                                     (long long)(f.file_off + layer_off + got), (long long)f.size);
+        if (k < 0) {
+            snprintf(buf, sizeof buf, "reading %s at %lld: %s", f.path.c_str(), (long long)(f.file_off + layer_off + got), strerror(errno));
+            *err = buf;
+            return DISSEM_EIO;
+        }
+        if (k == 0) {
+            snprintf(buf, sizeof buf, "%s ends at %lld, before the %lld bytes of the layer", f.path.c_str(),
+                     (long long)(f.file_off + layer_off + got), (long long)f.size);
+            *err = buf;
+            return DISSEM_EIO;
+        }
         got += k;
     }
+    return 0;
+}
+
+// One piece of the file into its staging slot.  A single pread() stream copies out of the page cache at a few GB/s,
+// far below what PCIe then carries; the piece is therefore read by `threads` threads, each its own 4 KiB-aligned share.
+static int pread_full(const FileSrc &f, uint8_t *dst, int64_t len, int64_t layer_off, int threads) {
+    constexpr int64_t kMinShare = 1 << 20;
+    int n = (int)std::min<int64_t>(std::max(threads, 1), len / kMinShare);
+    std::string err;
+    if (n <= 1) {
+        int rc = pread_range(f, dst, len, layer_off, &err);
+        return rc ? set_error(rc, "%s", err.c_str()) : 0;
+    }
+    const int64_t share = align_up((len + n - 1) / n, 4096);
+    std::vector<std::thread> pool;
+    std::vector<int> rcs((size_t)n, 0);
+    std::vector<std::string> errs((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        const int64_t a = std::min(len, i * share), b = std::min(len, (i + 1) * share);
+        pool.emplace_back([&, i, a, b] { rcs[i] = b > a ? pread_range(f, dst + a, b - a, layer_off + a, &errs[i]) : 0; });
+    }
+    for (auto &t : pool) t.join();
+    for (int i = 0; i < n; ++i)
+        if (rcs[i]) return set_error(rcs[i], "%s", errs[i].c_str());
     return 0;
 }
 
@@ -641,7 +675,7 @@ static int prepare_file_job(dissem_ctx *ctx, const dissem_xfer &x, FileJob *job)
 // Runs WITHOUT ctx->mu (other threads keep sending); the ring's own mutex serialises file transfers per GPU.
 // Pieces are cut at multiples of kStageBytes in LAYER space, so a piece covers whole checksum chunks except at the
 // fragment's own two ends; those entries are accumulated into, as for any single-fragment submission.
-static int stream_from_file(dissem_ctx *ctx, FileJob &job, const LaunchCfg &cfg_in, int64_t opt_unit_bytes) {
+static int stream_from_file(dissem_ctx *ctx, FileJob &job, const LaunchCfg &cfg_in, int64_t opt_unit_bytes, int file_threads) {
     DeviceState &ds = ctx->devs[job.dev_slot];
     std::lock_guard<std::mutex> ring_lock(*ds.ring_mu);
     int rc = ensure_ring(ds);
@@ -664,7 +698,7 @@ static int stream_from_file(dissem_ctx *ctx, FileJob &job, const LaunchCfg &cfg_
             r.in_flight[s] = false;
         }
         uint8_t *stage = r.slot[s] + (pos & 255);      // keep the piece's alignment (the kernel vectorises on layer offsets)
-        rc = pread_full(job.file, stage, len, pos);
+        rc = pread_full(job.file, stage, len, pos, file_threads);
         if (rc) return rc;
         XferDesc d;
         memset(&d, 0, sizeof d);
@@ -1286,6 +1320,7 @@ int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dis
     std::vector<FileJob> jobs;
     LaunchCfg cfg{};
     int64_t unit_bytes = 0;
+    int file_threads = 1;
     auto give_back = [&](std::vector<FileJob> &js) {                  // caller holds ctx->mu
         Ticket t;
         for (auto &j : js)
@@ -1310,12 +1345,13 @@ int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dis
         }
         cfg = LaunchCfg{0, (int)ctx->opt_ctas_per_sm, 0, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
         unit_bytes = ctx->opt_unit_bytes;
+        file_threads = (int)ctx->opt_file_threads;
     }
     Ticket ft;
     int rc = DISSEM_OK;
     for (auto &job : jobs) {
         cfg.n_sm = ctx->devs[job.dev_slot].n_sm;
-        rc = stream_from_file(ctx, job, cfg, unit_bytes);
+        rc = stream_from_file(ctx, job, cfg, unit_bytes, file_threads);
         if (rc) break;
     }
     if (rc == DISSEM_OK && !rest.empty()) rc = submit_compiled(ctx, rest.data(), (int)rest.size(), out);
@@ -1541,6 +1577,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     else if (k == "alloc_vmm") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0, 1 or 2"); ctx->opt_alloc_vmm = value; }
     else if (k == "mcast") { if (value < 0 || value > 3) return set_error(DISSEM_EINVAL, "mcast must be 0..3"); ctx->opt_mcast = value; }
     else if (k == "pull") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "pull must be 0, 1 or 2"); ctx->opt_pull = value; }
+    else if (k == "file_threads") { if (value < 1 || value > 64) return set_error(DISSEM_EINVAL, "file_threads must be 1..64"); ctx->opt_file_threads = value; }
     else if (k == "reg_cfg") { if (value < 0 || value > 9) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..9"); ctx->opt_reg_cfg = value; }
     else if (k == "unit_bytes") {
         if (value != 0 && (value < 4096 || value > DISSEM_CHUNK_BYTES || (value & (value - 1)))) return set_error(DISSEM_EINVAL, "unit_bytes must be 0 or a power of two in [4096, 262144]");
@@ -1569,6 +1606,7 @@ int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out) {
         if (!*value_out) ctx->mcast_note = why;
     }
     else if (k == "unit_bytes") *value_out = ctx->opt_unit_bytes;
+    else if (k == "file_threads") *value_out = ctx->opt_file_threads;
     else return set_error(DISSEM_EINVAL, "unknown option '%s'", key);
     return DISSEM_OK;
 }

@@ -78,7 +78,14 @@ func (t *DeviceTransport) Send(destID NodeID, message Message) error {
 			}
 		}
 		var ticket C.dissem_ticket
-		if rc := C.dissem_send(ctx, C.int(lm.SrcID), C.int(destID), C.int(lm.LayerID),
+		if lm.LayerSrc.Meta.Location == DiskLayer {
+			// transport.go:351-367: the layer is a file; it was registered with dissem_layer_attach_file(node, layer,
+			// LayerSrc.Fp, 0, DataSize) when CreateDiskLayer made it, and is streamed through pinned staging buffers
+			if rc := C.dissem_send_file(ctx, C.int(lm.SrcID), C.int(destID), C.int(lm.LayerID),
+				C.int64_t(lm.LayerSrc.Offset), C.int64_t(lm.LayerSrc.DataSize), C.int64_t(lm.TotalSize), &ticket); rc != 0 {
+				return derr("dissem_send_file")
+			}
+		} else if rc := C.dissem_send(ctx, C.int(lm.SrcID), C.int(destID), C.int(lm.LayerID),
 			C.int64_t(lm.LayerSrc.Offset), C.int64_t(lm.LayerSrc.DataSize), C.int64_t(lm.TotalSize), &ticket); rc != 0 {
 			return derr("dissem_send")
 		}

@@ -260,6 +260,7 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
  * read-only: "mcast_supported" (do all local GPUs support multicast objects), "mcast_groups" (multicast
  *  descriptors compiled so far),
  * "unit_bytes" (0 = auto; else power of two in [4096, 262144]),
+ * "file_threads" (1..64, default 8: threads that read one staged piece of a layer file in parallel, disk tier),
  * "pull" (0 = follow each transfer's DISSEM_XFER_PULL flag (default); 1 = pull every transfer: a process then
  *  executes the transfers whose DESTINATION node is local and needs the remote SOURCE layers imported;
  *  2 = push every transfer whatever its flag). */
