@@ -64,6 +64,7 @@ def load_library() -> ctypes.CDLL:
         "dissem_layer_read": (c.c_int, [P, c.c_int, c.c_int, P, i64, i64]),
         "dissem_host_alloc": (c.c_int, [c.POINTER(P), i64]),
         "dissem_host_free": (c.c_int, [P]),
+        "dissem_layer_reserve": (c.c_int, [P, c.c_int, i64, c.c_int]),
         "dissem_layer_attach_host": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
         "dissem_layer_attach_file": (c.c_int, [P, c.c_int, c.c_int, c.c_char_p, i64, i64]),
         "dissem_layer_detach_file": (c.c_int, [P, c.c_int, c.c_int]),
@@ -235,6 +236,10 @@ class Engine:
     # ---- store ----
     def alloc(self, node: int, layer: int, size: int):
         _check(lib().dissem_layer_alloc(self._ctx, node, layer, size))
+
+    def reserve(self, node: int, size: int, count: int = 1):
+        """Set aside destination buffers so that later alloc() calls of this size skip cudaMalloc."""
+        _check(lib().dissem_layer_reserve(self._ctx, node, size, count))
 
     def free(self, node: int, layer: int):
         _check(lib().dissem_layer_free(self._ctx, node, layer))

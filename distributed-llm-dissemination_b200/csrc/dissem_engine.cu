@@ -141,6 +141,8 @@ struct dissem_ctx {
     int64_t mcast_groups_compiled = 0;
     std::string mcast_note;
     std::vector<cudaEvent_t> event_pool[64];   // per device ordinal: events are reused across launches
+    // dissem_layer_reserve: destination buffers allocated ahead of time, keyed by (device ordinal, allocation bytes)
+    std::map<std::pair<int, int64_t>, std::vector<uint8_t *>> reserved;
     // options
     int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0, opt_alloc_vmm = 0, opt_mcast = 1, opt_file_threads = 8;
 };
@@ -832,6 +834,10 @@ int dissem_close(dissem_ctx *ctx) {
         for (auto &per_node : ctx->files)
             for (auto &kv : per_node)
                 if (kv.second.fd >= 0) close(kv.second.fd);
+        for (auto &kv : ctx->reserved) {
+            cudaSetDevice(kv.first.first);
+            for (uint8_t *p : kv.second) cudaFree(p);
+        }
         for (auto &ds : ctx->devs) {
             cudaSetDevice(ds.dev);
             for (int i = 0; i < kStageSlots; ++i) {
@@ -871,17 +877,46 @@ int dissem_layer_alloc(dissem_ctx *ctx, int node, int layer, int64_t size) {
         lb.vmm = true;
         lb.base = reinterpret_cast<uint8_t *>(lb.blk.va);
     } else {
-        void *p = nullptr;
-        cudaError_t e = cudaMalloc(&p, (size_t)lb.alloc_bytes());
-        if (e == cudaErrorMemoryAllocation) {
-            cudaGetLastError();
-            return set_error(DISSEM_ENOMEM, "out of HBM allocating %lld bytes for layer %d on node %d", (long long)lb.alloc_bytes(), layer, node);
+        auto rit = ctx->reserved.find(std::make_pair(ds->dev, lb.alloc_bytes()));
+        if (rit != ctx->reserved.end() && !rit->second.empty()) {
+            lb.base = rit->second.back();                 // set aside by dissem_layer_reserve: no cudaMalloc on this path
+            rit->second.pop_back();
+        } else {
+            void *p = nullptr;
+            cudaError_t e = cudaMalloc(&p, (size_t)lb.alloc_bytes());
+            if (e == cudaErrorMemoryAllocation) {
+                cudaGetLastError();
+                return set_error(DISSEM_ENOMEM, "out of HBM allocating %lld bytes for layer %d on node %d", (long long)lb.alloc_bytes(), layer, node);
+            }
+            CUDA_TRY(e);
+            lb.base = static_cast<uint8_t *>(p);
         }
-        CUDA_TRY(e);
-        lb.base = static_cast<uint8_t *>(p);
     }
     CUDA_TRY(cudaMemsetAsync(lb.base + lb.trailer_off(), 0, (size_t)lb.trailer_bytes(), ds->stream));
     ctx->layers[node][layer] = lb;
+    return DISSEM_OK;
+}
+
+int dissem_layer_reserve(dissem_ctx *ctx, int node, int64_t size, int count) {
+    if (!ctx || count < 0) return set_error(DISSEM_EINVAL, "dissem_layer_reserve: bad arguments");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceState *ds = nullptr;
+    int rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    LayerBuf shape;
+    shape.size = size < 0 ? 0 : size;
+    CUDA_TRY(cudaSetDevice(ds->dev));
+    auto &bucket = ctx->reserved[std::make_pair(ds->dev, shape.alloc_bytes())];
+    for (int i = 0; i < count; ++i) {
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, (size_t)shape.alloc_bytes());
+        if (e == cudaErrorMemoryAllocation) {
+            cudaGetLastError();
+            return set_error(DISSEM_ENOMEM, "out of HBM reserving %lld bytes on node %d's GPU", (long long)shape.alloc_bytes(), node);
+        }
+        CUDA_TRY(e);
+        bucket.push_back(static_cast<uint8_t *>(p));
+    }
     return DISSEM_OK;
 }
 

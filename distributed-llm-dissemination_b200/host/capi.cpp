@@ -268,6 +268,25 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
             if (rc) return rc;
         }
 
+    // Receive buffers for what the Assignment will deliver are set aside before the clock starts ("reserve":0 turns
+    // this off and leaves the allocation inside the send, where the reference has it: transport.go:201).
+    if (opt_i("reserve", 1) != 0) {
+        std::map<LayerID, int64_t> size_of;
+        for (auto &kv : leader_conf->InitialLayers) size_of[kv.first] = kv.second.LayerSize;
+        for (auto &n : cfg.Nodes)
+            for (auto &kv : n.InitialLayers) size_of.emplace(kv.first, kv.second.LayerSize);
+        for (auto &na : cfg.Assign) {
+            const NodeConf *nc = cfg.Node(na.first);
+            for (auto &la : na.second) {
+                const bool in_memory = !save_disk && nc && nc->InitialLayers.count(la.first);
+                auto so = size_of.find(la.first);
+                if (in_memory || so == size_of.end()) continue;
+                rc = dissem_layer_reserve(ctx, (int)na.first, so->second, 1);
+                if (rc) return rc;
+            }
+        }
+    }
+
     DeviceFabric fabric(ctx);
     fabric.pace = opt_i("pace", 0) != 0;
     std::vector<std::unique_ptr<DeviceTransport>> transports;

@@ -98,6 +98,12 @@ int dissem_n_nodes(dissem_ctx *ctx);
  * per-chunk checksum table and its received-bytes counter (both zeroed). */
 int dissem_layer_alloc(dissem_ctx *ctx, int node, int layer, int64_t size);
 int dissem_layer_free(dissem_ctx *ctx, int node, int layer);
+/* Set aside `count` buffers for layers of `size` bytes on `node`'s GPU.  A later dissem_layer_alloc of that size on that
+ * GPU (any of its nodes) takes one of them instead of calling cudaMalloc, which is most of what a small Transport.Send
+ * costs (~0.3 ms against ~0.04 ms for moving 1 MiB; the reference pays make([]byte, LayerSize) inside its clock too,
+ * transport.go:201).  A leader that knows the Assignment reserves before it starts the clock.  Unused buffers are
+ * released by dissem_close.  Not used for VMM-backed layers ("alloc_vmm"). */
+int dissem_layer_reserve(dissem_ctx *ctx, int node, int64_t size, int count);
 /* size_out / device_ptr_out may be NULL.  DISSEM_ENOENT if the node does not hold the layer. */
 int dissem_layer_info(dissem_ctx *ctx, int node, int layer, int64_t *size_out, void **device_ptr_out);
 /* Synthesise contents on the GPU (DISSEM_FILL_*); asynchronous on the node's stream. */

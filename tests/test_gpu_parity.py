@@ -715,3 +715,31 @@ def test_layer_beyond_4GiB_offsets():
         lo = (1 << 32) - 4096
         assert np.array_equal(eng.read(1, 2, off=lo, size=8192), data[lo:lo + 8192])
         assert np.array_equal(eng.read(1, 2, off=size - 4096, size=4096), data[-4096:])
+
+
+def test_reserved_destination_buffers():
+    """dissem_layer_reserve: buffers set aside ahead of time stand in for cudaMalloc in dissem_layer_alloc; a layer
+    allocated from them starts like any other (zero received counter and checksum table) and delivers bit-exactly."""
+    size = 3 * d.CHUNK_BYTES + 17
+    want = o.fill_bytes(o.FILL_PATTERN, 2, size, SEED)
+    with d.Engine([0, 0]) as eng:
+        eng.alloc(0, 2, size)
+        eng.fill(0, 2, d.FILL_PATTERN, SEED)
+        # dirty a buffer's trailer, give it back to the driver, then reserve: the reservation likely reuses that memory
+        eng.alloc(1, 99, size)
+        eng.alloc(1, 2, size)
+        eng.wait(eng.send(0, 1, 2, 0, size, size))
+        eng.free(1, 2)
+        eng.free(1, 99)
+        eng.reserve(1, size, 2)
+        for layer in (2, 3):
+            eng.alloc(1, layer, size)
+            assert eng.received(1, layer) == 0 and not eng.checksums(1, layer).any()
+        eng.alloc(1, 4, size)                                  # reservation used up: plain allocation again
+        eng.wait(eng.send(0, 1, 2, 0, size, size))
+        assert np.array_equal(eng.read(1, 2), want)
+        assert np.array_equal(eng.checksums(1, 2), o.checksum(want))
+        assert eng.received(1, 2) == size
+        eng.reserve(0, 1 << 20, 3)                             # left unused: released by close
+    r = host.run_distribution(o.config_ring_fixture(4, 300_001), 1, seed=SEED, timeout_ms=10000, reserve=0)
+    assert r["verified"] and r["ready_equals_assignment"]
