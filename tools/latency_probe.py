@@ -8,7 +8,6 @@ import time
 
 sys.path.insert(0, __file__.rsplit("/tools/", 1)[0])
 import dissem_b200 as d
-from oracle import dissem_oracle as o          # config text only
 
 host = importlib.import_module("distributed-llm-dissemination_b200.host")
 
@@ -44,7 +43,12 @@ def main():
         print(json.dumps({"what": "engine calls, one layer", "layer_bytes": size, "send+wait_us": send_wait * 1e6,
                           "layer_alloc_us": alloc * 1e6, "layer_alloc_from_reserve_us": alloc_reserved * 1e6,
                           "layer_free_us": free * 1e6}), flush=True)
-    text = o.config_readme()
+    text = json.dumps({          # the README's JSON (readme.md:17-64), flat schema
+        "Nodes": [{"Id": 0, "Addr": ":8080", "IsLeader": True, "InitialLayers": {"1": {}, "3": {}}},
+                  {"Id": 1, "Addr": ":8081", "IsLeader": False, "InitialLayers": {"1": {}}},
+                  {"Id": 2, "Addr": ":8082", "IsLeader": False, "InitialLayers": {}},
+                  {"Id": 3, "Addr": ":8083", "IsLeader": False, "InitialLayers": {"3": {}}}],
+        "Assignment": {"1": {"1": {}}, "2": {"1": {}, "3": {}}, "3": {"3": {}}}, "LayerSize": size})
     for mode in (0, 1, 2):                      # mode 3 cannot plan the README JSON: it names no NetworkBW
         for batched in (False, True):
             for reserve in (0, 1):
