@@ -204,3 +204,26 @@ def test_paced_sends_honour_limit_rate(mode):
     assert paced["time_to_deliver_ms"] < 20 * floor_ms
     assert fast["time_to_deliver_ms"] < paced["time_to_deliver_ms"]
     assert paced["launches"] > fast["launches"]
+
+
+def test_file_to_peer_gpu_and_disk_distribution_over_two_gpus(tmp_path):
+    """The source node's GPU reads the staged pieces over PCIe and writes them into a peer GPU's HBM over NVLink."""
+    if d.lib().dissem_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    size = STAGE + 5 * d.CHUNK_BYTES + 11
+    want = o.fill_bytes(o.FILL_PATTERN, 5, size, SEED)
+    path = _file_with(tmp_path, 0, 5, want)
+    with d.Engine([0, 1]) as eng:
+        eng.attach_file(0, 5, path, size)
+        eng.alloc(1, 5, size)
+        eng.fill(1, 5, d.FILL_POISON)
+        eng.wait(eng.submit([d.Xfer(0, 1, 5, d.XFER_FILE, 0, 1000, size), d.Xfer(0, 1, 5, d.XFER_FILE, 1000, size - 1000, size)]))
+        assert np.array_equal(eng.read(1, 5), want)
+        assert np.array_equal(eng.checksums(1, 5), o.checksum(want))
+        assert np.array_equal(eng.verify(1, 5), o.checksum(want))
+    text = o.config_ring_fixture(4, 300_001)
+    for mode, batched in ((1, False), (3, True)):
+        store = tmp_path / f"m{mode}"
+        r = host.run_distribution(text, mode, node_device=[i % 2 for i in range(5)], batched=batched, seed=SEED,
+                                  time_scale=1_000_000, flags=3, timeout_ms=20000, storage=str(store))
+        assert r["verified"] and r["ready_equals_assignment"]
