@@ -31,7 +31,7 @@ int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, in
         dissem_xfer &x = xfers[i];
         const int gs = gpu_of_node[x.src_node], gd = gpu_of_node[x.dst_node];
         x.flags &= ~DISSEM_XFER_PULL;
-        if (gs == gd) continue;
+        if (gs == gd || (x.flags & DISSEM_XFER_FILE)) continue;      // a disk copy is streamed by its own node's GPU
         const int64_t forward = std::max(egress[gs], ingress[gd]);
         const int64_t reverse = std::max(ingress[gs], egress[gd]);
         if (2 * reverse < forward) x.flags |= DISSEM_XFER_PULL;
@@ -68,11 +68,11 @@ int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **ou
         if (used[i]) continue;
         const dissem_xfer &x = in[i];
         used[i] = 1;
-        if (x.size <= 0) { res.push_back(x); continue; }
+        if (x.size <= 0 || (x.flags & DISSEM_XFER_FILE)) { res.push_back(x); continue; }    // disk sources are not relayed
         std::vector<int> dsts{x.dst_node};
         for (int j = i + 1; j < n; ++j) {
             const dissem_xfer &y = in[j];
-            if (!used[j] && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
+            if (!used[j] && !(y.flags & DISSEM_XFER_FILE) && y.src_node == x.src_node && y.layer == x.layer && y.off == x.off && y.size == x.size &&
                 y.total == x.total && y.dst_node != x.dst_node) {
                 dsts.push_back(y.dst_node);
                 used[j] = 1;

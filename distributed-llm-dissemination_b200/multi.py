@@ -22,7 +22,8 @@ def device_of_node(n_nodes: int, owner: Callable[[int], int], rank: int, local_d
 def _sides(x, pull):
     """(executing node, other node) of a transfer: the source pushes unless the transfer is flagged PULL
     (DISSEM_XFER_PULL, set by dissem_plan_directions) or `pull` forces it."""
-    is_pull = bool(pull) or bool(getattr(x, "flags", 0) & 1)
+    flags = getattr(x, "flags", 0)
+    is_pull = (bool(pull) or bool(flags & 1)) and not (flags & 2)        # a disk source (DISSEM_XFER_FILE) always pushes
     return (x.dst_node, x.src_node) if is_pull else (x.src_node, x.dst_node)
 
 

@@ -352,3 +352,21 @@ def test_pace_schedule_edge_cases():
         host.pace_schedule(-1, 10, 10)
     with pytest.raises(ValueError):
         o.limiter_write_times(10, 0)
+
+
+def test_disk_sources_are_never_pulled_or_relayed():
+    """DISSEM_XFER_FILE: the node that holds the file streams it; the scheduling decisions leave such transfers alone."""
+    multi = importlib.import_module("distributed-llm-dissemination_b200.multi")
+    S = 8 << 20
+    xs = [d.Xfer(0, n, 7, d.XFER_FILE, 0, S, S) for n in (1, 2, 3)] + [d.Xfer(0, n, 8, 0, 0, S, S) for n in (1, 2, 3)]
+    out = d.plan_directions(xs, [0, 1, 2, 3])
+    assert [x.flags for x in out[:3]] == [d.XFER_FILE] * 3               # single seed: everything else is pulled
+    assert all(x.flags & d.XFER_PULL for x in out[3:])
+    relayed = d.plan_relay(xs, 4)
+    files = [x for x in relayed if x.flags & d.XFER_FILE]
+    assert [(x.src_node, x.dst_node, x.off, x.size, x.flags) for x in files] == [(0, n, 0, S, d.XFER_FILE) for n in (1, 2, 3)]
+    assert any(x.src_node != 0 for x in relayed if x.layer == 8)         # the HBM-resident layer is chained
+    owner = multi.owner_round_robin(4)
+    both = d.Xfer(0, 1, 7, d.XFER_FILE | d.XFER_PULL, 0, S, S)
+    assert multi.my_transfers([both], owner, 0) == [both] and multi.my_transfers([both], owner, 1) == []
+    assert multi.imports_needed([both], owner, 0) == [(1, 7, S)] and multi.exports_needed([both], owner, 1) == [(1, 7, S)]
