@@ -1389,7 +1389,17 @@ int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dis
         rc = stream_from_file(ctx, job, cfg, unit_bytes, file_threads);
         if (rc) break;
     }
-    if (rc == DISSEM_OK && !rest.empty()) rc = submit_compiled(ctx, rest.data(), (int)rest.size(), out);
+    if (rc == DISSEM_OK && !rest.empty()) {
+        // "behind them" on every GPU, not only on the streams that carried the files: a transfer of the rest may forward
+        // what a disk transfer has just loaded into another node's HBM (dissem_plan_optimize plans exactly that)
+        for (auto &ds : ctx->devs) {
+            cudaSetDevice(ds.dev);
+            for (auto &job : jobs)
+                if (rc == DISSEM_OK && cudaStreamWaitEvent(ds.stream, job.tp.end, 0) != cudaSuccess)
+                    rc = set_error(DISSEM_ECUDA, "cudaStreamWaitEvent: %s", cudaGetErrorString(cudaGetLastError()));
+        }
+        if (rc == DISSEM_OK) rc = submit_compiled(ctx, rest.data(), (int)rest.size(), out);
+    }
     std::lock_guard<std::mutex> lk(ctx->mu);
     if (rc) {
         // what was enqueued drains on its own; the events go back once the streams are idle

@@ -102,6 +102,31 @@ int dissem_plan_optimize(const dissem_xfer *in, int n, const int *gpu_of_node, i
     for (int i = 0; i < n; ++i)
         if (in[i].src_node < 0 || in[i].src_node >= n_nodes || in[i].dst_node < 0 || in[i].dst_node >= n_nodes)
             return set_error(DISSEM_ENOENT, "transfer %d names a node outside [0,%d)", i, n_nodes);
+    // Disk sources (DISSEM_XFER_FILE): a layer that several nodes need is read from its file ONCE, into the first of
+    // them; the others take it from that node's HBM, one round later (NVLink is ~16x the disk path).  Those forwards
+    // are ordinary fan-out transfers, so the relay decision below applies to them as well.
+    std::vector<dissem_xfer> staged(in, in + n);
+    bool any_file = false;
+    {
+        std::vector<char> seen((size_t)std::max(n, 1), 0);
+        for (int i = 0; i < n; ++i) {
+            if (seen[i] || !(staged[i].flags & DISSEM_XFER_FILE)) continue;
+            any_file = true;
+            const dissem_xfer first = staged[i];
+            if (first.size <= 0 || first.dst_node == first.src_node) continue;      // a node loading its own copy feeds nobody else
+            for (int j = i + 1; j < n; ++j) {
+                dissem_xfer &y = staged[j];
+                if (!seen[j] && (y.flags & DISSEM_XFER_FILE) && y.src_node == first.src_node && y.layer == first.layer &&
+                    y.off == first.off && y.size == first.size && y.total == first.total && y.dst_node != first.dst_node &&
+                    y.dst_node != first.src_node) {
+                    seen[j] = 1;
+                    y.src_node = first.dst_node;
+                    y.flags &= ~DISSEM_XFER_FILE;
+                }
+            }
+        }
+    }
+    in = staged.data();
     // busiest-port bytes of a transfer list (transfers inside one GPU do not use a port)
     auto busiest = [&](const dissem_xfer *xs, int cnt) {
         std::map<int, int64_t> eg, ing;
@@ -154,6 +179,12 @@ int dissem_plan_optimize(const dissem_xfer *in, int n, const int *gpu_of_node, i
     }
     int rc = dissem_plan_directions(chosen, n_chosen, gpu_of_node, n_nodes);
     if (rc) { free(chosen); return rc; }
+    if (any_file)                 // everything that is not read from disk runs after the disk transfers (round 0)
+        for (int i = 0; i < n_chosen; ++i)
+            if (!(chosen[i].flags & DISSEM_XFER_FILE)) {
+                const int r = (chosen[i].flags >> DISSEM_XFER_ROUND_SHIFT) & 0xFFFF;
+                chosen[i].flags = (chosen[i].flags & ~(0xFFFF << DISSEM_XFER_ROUND_SHIFT)) | DISSEM_XFER_ROUND(r + 1);
+            }
     *out = chosen;
     *n_out = n_chosen;
     if (relay_pieces_out) *relay_pieces_out = pieces_used;

@@ -160,7 +160,6 @@ int DeviceTransport::Send(NodeID dest, MessagePtr message) {
 
 int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *device_ms_out) {
     std::vector<dissem_xfer> xs;
-    bool any_file = false;
     // which sources are disk copies is settled before any destination buffer is created (a node may load its own file)
     std::vector<int> from_file;
     for (auto &x : xfers)
@@ -174,11 +173,7 @@ int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *de
         d.dst_node = (int32_t)x.Dest;
         d.layer = (int32_t)x.Layer;
         // a source that holds the layer on disk only (DiskLayer) is read from its file
-        d.flags = 0;
-        if (from_file[xs.size()]) {
-            d.flags = DISSEM_XFER_FILE;
-            any_file = true;
-        }
+        d.flags = from_file[xs.size()] ? DISSEM_XFER_FILE : 0;
         d.off = x.Offset;
         d.size = x.DataSize;
         d.total = x.TotalSize;
@@ -196,15 +191,11 @@ int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *de
     int n_opt = 0;
     int rc = 0;
     dissem_ticket ticket = 0;
-    if (any_file) {
-        // relay chains and pulls assume HBM-resident sources: a plan with disk sources is submitted as planned
-        rc = dissem_schedule_submit(fabric_->ctx(), xs.data(), (int)xs.size(), &ticket);
-    } else {
-        rc = dissem_plan_optimize(xs.data(), (int)xs.size(), gpu_of_node.data(), n_nodes, &opt, &n_opt, nullptr);
-        if (rc) return rc;
-        rc = dissem_schedule_submit(fabric_->ctx(), opt, n_opt, &ticket);
-        free(opt);
-    }
+    // relay chains, push/pull directions, and for disk sources "read the file once, forward from HBM"
+    rc = dissem_plan_optimize(xs.data(), (int)xs.size(), gpu_of_node.data(), n_nodes, &opt, &n_opt, nullptr);
+    if (rc) return rc;
+    rc = dissem_schedule_submit(fabric_->ctx(), opt, n_opt, &ticket);
+    free(opt);
     if (rc) return rc;
     double ms = 0.0;
     rc = dissem_wait(fabric_->ctx(), ticket, &ms);

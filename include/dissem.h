@@ -206,6 +206,9 @@ int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **ou
  * relay chains when the plan has fan-out and the busiest NVLink port gets at least 10 % less to carry that way
  * (pieces of about 64 MiB; the port load is scaled by the pipeline-fill factor (rounds / pieces)), then
  * dissem_plan_directions on whatever was chosen.  *relay_pieces_out (may be NULL): pieces used, 0 = no relay.
+ * Disk sources (DISSEM_XFER_FILE): a layer that several nodes need keeps ONE transfer from the file (to the first of them,
+ * round 0); the other destinations are fed from that node's HBM, and every transfer that is not read from disk is moved
+ * one round later, so that a caller who submits one round per call (several processes) keeps the order too.
  * *out is malloc'ed (dissem_free).  Pure host logic. */
 int dissem_plan_optimize(const dissem_xfer *in, int n, const int *gpu_of_node, int n_nodes, dissem_xfer **out, int *n_out,
                          int *relay_pieces_out);

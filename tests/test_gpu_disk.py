@@ -227,3 +227,37 @@ def test_file_to_peer_gpu_and_disk_distribution_over_two_gpus(tmp_path):
         r = host.run_distribution(text, mode, node_device=[i % 2 for i in range(5)], batched=batched, seed=SEED,
                                   time_scale=1_000_000, flags=3, timeout_ms=20000, storage=str(store))
         assert r["verified"] and r["ready_equals_assignment"]
+
+
+def test_disk_layer_read_once_then_forwarded(tmp_path):
+    """dissem_plan_optimize on a disk layer with three destinations: one file read, the rest forwarded from HBM; the
+    engine starts the forwards only after the disk transfer has landed (also when they run on another GPU)."""
+    n_gpu = max(1, min(d.lib().dissem_device_count(), 2))
+    size = STAGE + 9 * d.CHUNK_BYTES + 5
+    want = o.fill_bytes(o.FILL_PATTERN, 7, size, SEED)
+    path = _file_with(tmp_path, 0, 7, want)
+    gpus = [0, 1 % n_gpu, 0, 1 % n_gpu]
+    with d.Engine(gpus) as eng:
+        eng.attach_file(0, 7, path, size)
+        for n in (1, 2, 3):
+            eng.alloc(n, 7, size)
+        plan, _ = d.plan_optimize([d.Xfer(0, n, 7, d.XFER_FILE, 0, size, size) for n in (1, 2, 3)], gpus)
+        assert sum(1 for x in plan if x.flags & d.XFER_FILE) == 1
+        for rep in range(3):
+            for n in (1, 2, 3):
+                eng.fill(n, 7, d.FILL_POISON)
+            eng.wait(eng.submit(plan))
+            for n in (1, 2, 3):
+                assert np.array_equal(eng.read(n, 7), want), (rep, n)
+                assert np.array_equal(eng.checksums(n, 7), o.checksum(want)), (rep, n)
+
+
+def test_batched_distribution_from_disk_with_fanout(tmp_path):
+    """The batched leader hands a plan with disk sources to dissem_plan_optimize: layers assigned to several nodes."""
+    size = 300_001
+    conf = json.loads(o.config_identity_fixture(4, size))
+    conf["Assignment"] = {"1": {"1": {}, "2": {}}, "2": {"1": {}, "2": {}}, "3": {"1": {}, "3": {}}, "4": {"4": {}}}
+    text = json.dumps(conf)
+    for batched in (True, False):
+        r = host.run_distribution(text, 0, batched=batched, seed=SEED, timeout_ms=20000, storage=str(tmp_path / str(batched)))
+        assert r["verified"] and r["ready_equals_assignment"] and r["layers_checked"] == 7

@@ -370,3 +370,24 @@ def test_disk_sources_are_never_pulled_or_relayed():
     both = d.Xfer(0, 1, 7, d.XFER_FILE | d.XFER_PULL, 0, S, S)
     assert multi.my_transfers([both], owner, 0) == [both] and multi.my_transfers([both], owner, 1) == []
     assert multi.imports_needed([both], owner, 0) == [(1, 7, S)] and multi.exports_needed([both], owner, 1) == [(1, 7, S)]
+
+
+def test_plan_optimize_reads_a_disk_layer_once():
+    """A layer on disk that several nodes need: one transfer keeps DISSEM_XFER_FILE, the other destinations are fed from
+    the first one's HBM in later rounds; every destination still receives every byte exactly once."""
+    S = 200 << 20
+    xs = [d.Xfer(0, n, 7, d.XFER_FILE, 0, S, S) for n in (1, 2, 3)] + [d.Xfer(0, 0, 9, d.XFER_FILE, 0, S, S), d.Xfer(0, 2, 9, d.XFER_FILE, 0, S, S)]
+    for gpus in ([0, 1, 2, 3], [0, 0, 0, 0]):
+        out, _ = d.plan_optimize(xs, gpus)
+        files = [(x.src_node, x.dst_node, x.layer) for x in out if x.flags & d.XFER_FILE]
+        assert files == [(0, 1, 7), (0, 0, 9), (0, 2, 9)]                 # a node loading its own copy feeds nobody
+        assert all(d.xfer_round(x) == 0 for x in out if x.flags & d.XFER_FILE)
+        rest = [x for x in out if not x.flags & d.XFER_FILE]
+        assert rest and all(d.xfer_round(x) >= 1 and x.src_node in (1, 2, 3) and x.layer == 7 for x in rest)
+        for dst in (2, 3):
+            got = sorted((x.off, x.size) for x in rest if x.dst_node == dst)
+            assert got[0][0] == 0 and sum(sz for _, sz in got) == S
+            assert all(a + n == b for (a, n), (b, _) in zip(got[:-1], got[1:]))
+    # without disk sources nothing is shifted
+    plain, _ = d.plan_optimize([d.Xfer(0, n, 7, 0, 0, 1 << 20, 1 << 20) for n in (1, 2)], [0, 1, 2])
+    assert all(d.xfer_round(x) == 0 for x in plain)
