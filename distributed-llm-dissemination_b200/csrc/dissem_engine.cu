@@ -1384,10 +1384,37 @@ int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dis
     }
     Ticket ft;
     int rc = DISSEM_OK;
-    for (auto &job : jobs) {
-        cfg.n_sm = ctx->devs[job.dev_slot].n_sm;
-        rc = stream_from_file(ctx, job, cfg, unit_bytes, file_threads);
-        if (rc) break;
+    // Files held by nodes of different GPUs go up different PCIe links: one streaming thread per GPU, each working
+    // through its own jobs in order; the reader threads are shared out so that the host cores are not oversubscribed.
+    std::vector<int> slots;
+    for (auto &job : jobs)
+        if (std::find(slots.begin(), slots.end(), job.dev_slot) == slots.end()) slots.push_back(job.dev_slot);
+    auto run_slot = [&](int slot, int readers, int *rc_out, std::string *err_out) {
+        for (auto &job : jobs) {
+            if (job.dev_slot != slot) continue;
+            LaunchCfg c = cfg;
+            c.n_sm = ctx->devs[slot].n_sm;
+            const int r = stream_from_file(ctx, job, c, unit_bytes, readers);
+            if (r) {                                   // the error text is thread-local: carry it to the caller
+                *rc_out = r;
+                *err_out = last_error();
+                return;
+            }
+        }
+    };
+    if (slots.size() <= 1) {
+        std::string err;
+        if (!slots.empty()) run_slot(slots[0], file_threads, &rc, &err);
+    } else {
+        const int cores = (int)std::max(1u, std::thread::hardware_concurrency());
+        const int readers = std::max(1, std::min(file_threads, cores / (int)slots.size()));
+        std::vector<int> rcs(slots.size(), 0);
+        std::vector<std::string> errs(slots.size());
+        std::vector<std::thread> streamers;
+        for (size_t i = 0; i < slots.size(); ++i) streamers.emplace_back(run_slot, slots[i], readers, &rcs[i], &errs[i]);
+        for (auto &t : streamers) t.join();
+        for (size_t i = 0; i < slots.size(); ++i)
+            if (rcs[i] && !rc) rc = set_error(rcs[i], "%s", errs[i].c_str());
     }
     if (rc == DISSEM_OK && !rest.empty()) {
         // "behind them" on every GPU, not only on the streams that carried the files: a transfer of the rest may forward

@@ -221,6 +221,27 @@ def test_file_to_peer_gpu_and_disk_distribution_over_two_gpus(tmp_path):
         assert np.array_equal(eng.read(1, 5), want)
         assert np.array_equal(eng.checksums(1, 5), o.checksum(want))
         assert np.array_equal(eng.verify(1, 5), o.checksum(want))
+    # files of nodes on different GPUs in one plan: streamed concurrently, one thread per GPU
+    other = o.fill_bytes(o.FILL_PATTERN, 6, size, SEED)
+    path6 = _file_with(tmp_path, 1, 6, other)
+    with d.Engine([0, 1]) as eng:
+        eng.attach_file(0, 5, path, size)
+        eng.attach_file(1, 6, path6, size)
+        for node in (0, 1):
+            eng.alloc(node, 5, size)
+            eng.alloc(node, 6, size)
+        plan = [d.Xfer(0, 1, 5, d.XFER_FILE, 0, size, size), d.Xfer(1, 0, 6, d.XFER_FILE, 0, size, size),
+                d.Xfer(0, 0, 5, d.XFER_FILE, 0, size, size), d.Xfer(1, 1, 6, d.XFER_FILE, 0, size, size)]
+        for _ in range(2):
+            eng.wait(eng.submit(plan))
+            for node in (0, 1):
+                assert np.array_equal(eng.read(node, 5), want) and np.array_equal(eng.read(node, 6), other)
+                assert np.array_equal(eng.checksums(node, 5), o.checksum(want))
+                assert np.array_equal(eng.checksums(node, 6), o.checksum(other))
+        with pytest.raises(d.DissemError) as e:                  # an error inside a streaming thread reaches the caller
+            os.truncate(path6, size // 2)
+            eng.wait(eng.submit(plan))
+        assert e.value.code == -11 and "ends at" in str(e.value)
     text = o.config_ring_fixture(4, 300_001)
     for mode, batched in ((1, False), (3, True)):
         store = tmp_path / f"m{mode}"

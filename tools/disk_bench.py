@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--dir", default="/tmp")
     ap.add_argument("--threads", default="1,2,4,8,16")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--gpus", type=int, default=8, help="also load one file per GPU concurrently on up to this many GPUs")
     args = ap.parse_args()
     size = args.size
     path = os.path.join(args.dir, f"dissem_disk_bench_{os.getpid()}.layer")
@@ -74,6 +75,43 @@ def main():
             print(json.dumps({"case": "file -> staging ring -> HBM", "file_threads": th, "bytes": size, "best_s": best,
                               "GBps": size / best / 1e9, "verified": ok, "host_cores": os.cpu_count()}), flush=True)
     os.unlink(path)
+    # several GPUs: one file per GPU, each loaded into a node of its own GPU, all in one submitted plan
+    n_gpu = d.lib().dissem_device_count()
+    if args.gpus > 1 and n_gpu >= 2:
+        n = min(args.gpus, n_gpu)
+        per = size // 2
+        paths = []
+        with d.Engine(list(range(n))) as eng:
+            hb = d.HostBuffer(per)
+            try:
+                eng.alloc(0, 100, per)
+                eng.fill(0, 100, d.FILL_PATTERN, 0x5EED)
+                ref = eng.verify(0, 100)
+                d.lib().dissem_layer_read(eng._ctx, 0, 100, hb.ptr, 0, per)
+                for g in range(n):
+                    p = os.path.join(args.dir, f"dissem_disk_bench_{os.getpid()}_{g}.layer")
+                    with open(p, "wb") as f:
+                        f.write(memoryview(hb.array))
+                    paths.append(p)
+                eng.free(0, 100)
+            finally:
+                hb.free()
+            for g in range(n):
+                eng.attach_file(g, 100, paths[g], per)
+                eng.alloc(g, 100, per)
+            for k in sorted({1, 2, n}):
+                plan = [d.Xfer(g, g, 100, d.XFER_FILE, 0, per, per) for g in range(k)]
+                best = 1e9
+                for _ in range(args.reps):
+                    t0 = time.perf_counter()
+                    eng.wait(eng.submit(plan))
+                    best = min(best, time.perf_counter() - t0)
+                ok = all(bool((eng.checksums(g, 100) == ref).all()) for g in range(k))
+                print(json.dumps({"case": "one file per GPU, loaded concurrently", "gpus_loading": k, "bytes_each": per,
+                                  "best_s": best, "aggregate_GBps": k * per / best / 1e9, "verified": ok,
+                                  "host_cores": os.cpu_count()}), flush=True)
+        for p in paths:
+            os.unlink(p)
 
 
 if __name__ == "__main__":
