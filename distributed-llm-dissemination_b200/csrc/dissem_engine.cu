@@ -639,6 +639,7 @@ struct FileJob {
     uint8_t *dst = nullptr;
     unsigned long long *csum = nullptr, *received = nullptr;
     TicketPart tp{-1, nullptr, nullptr, nullptr};
+    bool owns_fd = false;             // file.fd is a dup() made for this transfer; dissem_schedule_submit closes it
 };
 
 // caller holds ctx->mu
@@ -651,6 +652,10 @@ static int prepare_file_job(dissem_ctx *ctx, const dissem_xfer &x, FileJob *job)
     if (fit == ctx->files[x.src_node].end()) return set_error(DISSEM_ENOENT, "node %d holds no disk copy of layer %d", x.src_node, x.layer);
     job->x = x;
     job->file = fit->second;
+    // the transfer reads through its own descriptor: a concurrent dissem_layer_detach_file cannot pull the file away
+    job->file.fd = dup(fit->second.fd);
+    if (job->file.fd < 0) return set_error(DISSEM_EIO, "dup(%s): %s", fit->second.path.c_str(), strerror(errno));
+    job->owns_fd = true;
     job->dev_slot = ctx->node_dev_slot[x.src_node];              // attach_file accepts local nodes only
     LayerBuf *dst = nullptr;
     rc = find_layer(ctx, x.dst_node, x.layer, &dst);
@@ -1353,6 +1358,13 @@ int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dis
     // the rest of the plan is launched behind them, and one ticket covers both.
     std::vector<dissem_xfer> rest;
     std::vector<FileJob> jobs;
+    struct CloseFds {
+        std::vector<FileJob> &js;
+        ~CloseFds() {
+            for (auto &j : js)
+                if (j.owns_fd) close(j.file.fd);
+        }
+    } close_fds{jobs};
     LaunchCfg cfg{};
     int64_t unit_bytes = 0;
     int file_threads = 1;

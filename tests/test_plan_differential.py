@@ -1,0 +1,94 @@
+"""Differential tests of the plan generators: the C++ mirror (host/plan.cpp, host/flow.cpp, through dissem_plan_json)
+against the independent numpy/Python restatement in oracle/, on RANDOM configurations (hypothesis, derandomised so the
+suite is reproducible).  Either both reject a configuration or both produce the same transfers, t and self jobs."""
+import json
+
+import pytest
+from hypothesis import HealthCheck, given, settings
+from hypothesis import strategies as st
+
+import dissem_b200 as d
+from oracle import dissem_oracle as o
+
+
+@st.composite
+def configs(draw, need_bw=False):
+    n_nodes = draw(st.integers(2, 6))
+    n_layers = draw(st.integers(1, 7))
+    sizes = [draw(st.sampled_from([1, 17, 4096, 262144, 262145, 1 << 20, 3_000_001, 67_108_864])) for _ in range(n_layers)]
+    rates = st.sampled_from([1_000, 77_777, 1 << 20, 209_715_200, 900_000_000_000])
+    nodes = []
+    for i in range(n_nodes):
+        held = [l for l in range(n_layers) if draw(st.integers(0, 9)) < (8 if i == 0 else 3)]
+        nodes.append({"Id": i, "Addr": f"gpu:{i}", "NetworkBW": draw(rates), "IsLeader": i == 0,
+                      "Sources": {"2": draw(rates) if need_bw or draw(st.booleans()) else 0},
+                      "InitialLayers": {"2": {str(l): {"LayerSize": sizes[l]} for l in held}}})
+    assignment = {}
+    for i in range(n_nodes):
+        want = [l for l in range(n_layers) if draw(st.integers(0, 9)) < 4]
+        if want:
+            assignment[str(i)] = {str(l): {} for l in want}
+    return json.dumps({"Nodes": nodes, "Assignment": assignment})
+
+
+def _rows(plan):
+    return [tuple(x[:6]) for x in plan["xfers"]]
+
+
+def _orows(xs):
+    return [(x.src, x.dst, x.layer, x.off, x.size, x.total) for x in xs]
+
+
+def _both(cpp, orc):
+    """Run both sides; a rejection on one side must be a rejection on the other."""
+    try:
+        want = orc()
+    except (ValueError, KeyError) as e:
+        with pytest.raises(d.DissemError):
+            cpp()
+        return None, None
+    return cpp(), want
+
+
+COMMON = dict(max_examples=120, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow])
+
+
+@settings(**COMMON)
+@given(configs())
+def test_mode0_random_configs(text):
+    got, want = _both(lambda: d.plan(text, 0), lambda: o.plan_mode0(o.parse_config(text)))
+    if got is not None:
+        assert _rows(got) == _orows(want)
+
+
+@settings(**COMMON)
+@given(configs(), st.integers(0, 2**64 - 1), st.sampled_from([0, 1]))
+def test_mode1_random_configs(text, seed, policy):
+    got, want = _both(lambda: d.plan(text, 1, seed=seed, policy=policy),
+                      lambda: o.plan_mode1(o.parse_config(text), seed=seed, policy="balanced" if policy else "random"))
+    if got is not None:
+        assert _rows(got) == _orows(want)
+        cand = o.mode1_owner_candidates(o.parse_config(text))
+        assert all(s in cand[(dst, l)] for (s, dst, l, *_r) in _rows(got))
+
+
+@settings(**COMMON)
+@given(configs())
+def test_mode2_initial_jobs_random_configs(text):
+    got, want = _both(lambda: d.plan(text, 2), lambda: o.plan_mode2_initial(o.parse_config(text)))
+    if got is not None:
+        assert _rows(got) == _orows(want)
+
+
+@settings(**COMMON)
+@given(configs(need_bw=True), st.sampled_from([1, 1000, 1_000_000]), st.sampled_from([0, 1, 2, 3, 6, 7]))
+def test_mode3_random_configs(text, scale, flags):
+    kw = dict(time_scale=scale, zero_rate_unlimited=bool(flags & 1), sizes_from_announces=bool(flags & 2), multi_dest=bool(flags & 4))
+    got, want = _both(lambda: d.plan(text, 3, time_scale=scale, flags=flags), lambda: o.plan_mode3(o.parse_config(text), **kw))
+    if got is not None:
+        t, xs, self_jobs = want
+        assert got["t"] == t and _rows(got) == _orows(xs)
+        assert [tuple(j) for j in got["self_jobs"]] == [(n, l, s) for (n, l, s, _off) in self_jobs]
+        # every fragment list tiles what it delivers, and rates are dataSize * ticks-per-second / t (node.go:1281)
+        for x in got["xfers"]:
+            assert x[6] == (x[4] * scale // t if t > 0 else 0)
