@@ -743,3 +743,52 @@ def test_reserved_destination_buffers():
         eng.reserve(0, 1 << 20, 3)                             # left unused: released by close
     r = host.run_distribution(o.config_ring_fixture(4, 300_001), 1, seed=SEED, timeout_ms=10000, reserve=0)
     assert r["verified"] and r["ready_equals_assignment"]
+
+
+@pytest.mark.parametrize("case", range(10))
+def test_random_fragment_plans_match_oracle(case):
+    """Seeded random plans: ragged layer sizes, every destination copy tiled by fragments cut at random BYTES from
+    random holders, random kernel variant / unit size / push-pull flags; the store must equal the oracle's byte for
+    byte (gaps stay poison) and every fused table the oracle's checksum of what actually landed."""
+    rng = np.random.default_rng(1000 + case)
+    n_gpu = max(1, min(d.lib().dissem_device_count(), 2))
+    n_nodes = 5
+    sizes = {l: int(rng.choice([1, 37, 4095, 262144, 262147, 777_777, (1 << 20) + 13, 3 * (1 << 20) + 5])) for l in range(6)}
+    holders = {l: sorted(rng.choice(n_nodes, size=int(rng.integers(1, 4)), replace=False).tolist()) for l in sizes}
+    with d.Engine([n % n_gpu for n in range(n_nodes)]) as eng:
+        eng.set_option("variant", int(rng.integers(0, 2)))
+        eng.set_option("unit_bytes", int(rng.choice([0, 4096, 32768, 262144])))
+        store = {}
+        for l, hs in holders.items():
+            for h in hs:
+                eng.alloc(h, l, sizes[l])
+                eng.fill(h, l, d.FILL_PATTERN, SEED)
+                store[(h, l)] = o.fill_bytes(o.FILL_PATTERN, l, sizes[l], SEED)
+        plan, oplan = [], []
+        for l, hs in holders.items():
+            for dst in range(n_nodes):
+                if dst in hs or rng.random() < 0.4:
+                    continue
+                eng.alloc(dst, l, sizes[l])
+                eng.fill(dst, l, d.FILL_POISON)
+                eng.reset(dst, l)
+                k = int(rng.integers(1, 5))
+                cuts = sorted(set([0, sizes[l]] + rng.integers(0, sizes[l] + 1, size=k).tolist()))
+                for a, b in zip(cuts[:-1], cuts[1:]):
+                    if rng.random() < 0.15:
+                        continue                                   # leave a hole: those bytes must stay poison
+                    src = int(rng.choice(hs))
+                    plan.append(d.Xfer(src, dst, l, d.XFER_PULL if rng.random() < 0.3 else 0, a, b - a, sizes[l]))
+                    oplan.append(o.Xfer(src, dst, l, a, b - a, sizes[l]))
+        eng.wait(eng.submit(plan))
+        want = o.apply_transfers(store, oplan)
+        landed = {}
+        for x in oplan:
+            landed.setdefault((x.dst, x.layer), np.zeros((sizes[x.layer] + d.CHUNK_BYTES - 1) // d.CHUNK_BYTES * 2, dtype=np.uint64).reshape(-1, 2))
+            with np.errstate(over="ignore"):
+                landed[(x.dst, x.layer)] += o.checksum_fragment(store[(x.src, x.layer)][x.off:x.off + x.size], x.off, x.total)
+        for (node, l), data in want.items():
+            assert np.array_equal(eng.read(node, l), data), (case, node, l)
+        for key, cs in landed.items():
+            assert np.array_equal(eng.checksums(*key), cs), (case, key)
+            assert eng.received(*key) == sum(x.size for x in oplan if (x.dst, x.layer) == key)
