@@ -5,7 +5,7 @@ from __future__ import annotations
 import ctypes
 import os
 import subprocess
-from typing import List, Sequence
+from typing import Sequence
 
 import numpy as np
 

@@ -3,7 +3,6 @@ what.  No GPU, no compute entry point."""
 import importlib
 import os
 import socket
-import sys
 
 import pytest
 import torch.distributed as dist

@@ -12,7 +12,6 @@ import sys
 import time
 
 sys.path.insert(0, __file__.rsplit("/tools/", 1)[0])
-import numpy as np
 
 import dissem_b200 as d
 

@@ -9,7 +9,6 @@ import importlib
 import json
 import os
 import sys
-import time
 
 sys.path.insert(0, __file__.rsplit("/tools/", 1)[0])
 import torch
