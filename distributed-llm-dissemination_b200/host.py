@@ -27,6 +27,8 @@ def _bind():
         L.dissem_run_json.argtypes = [c.c_char_p, c.c_int, c.POINTER(c.c_int), c.c_char_p, c.POINTER(c.c_void_p)]
         L.dissem_msg_roundtrip_json.restype = c.c_int
         L.dissem_msg_roundtrip_json.argtypes = [c.c_char_p, c.POINTER(c.c_void_p), c.POINTER(c.c_void_p)]
+        L.dissem_transport_script_json.restype = c.c_int
+        L.dissem_transport_script_json.argtypes = [c.c_char_p, c.POINTER(c.c_void_p)]
         L.dissem_pace_schedule.restype = c.c_int
         L.dissem_pace_schedule.argtypes = [c.c_int64, c.c_int64, c.c_int64, c.POINTER(c.c_int64), c.POINTER(c.c_int64),
                                            c.POINTER(c.c_int64), c.c_int, c.POINTER(c.c_int)]
@@ -66,6 +68,17 @@ def run_distribution(config_json: str, mode: int, node_device: Optional[Sequence
     if node_device is not None:
         arr = (ctypes.c_int * len(node_device))(*node_device)
     rc = L.dissem_run_json(config_json.encode(), mode, arr, json.dumps(opts).encode(), ctypes.byref(out))
+    if rc != 0:
+        raise HostError(rc, (L.dissem_last_error() or b"").decode())
+    return json.loads(_take(L, out))
+
+
+def transport_script(peers: Sequence[int], ops: Sequence[dict]) -> dict:
+    """Drive the device transport's control plane (Send / Broadcast / Close / RegisterPipe) and return what every peer's
+    Deliver() yields, in order.  Needs no GPU."""
+    L = _bind()
+    out = ctypes.c_void_p()
+    rc = L.dissem_transport_script_json(json.dumps({"peers": list(peers), "ops": list(ops)}).encode(), ctypes.byref(out))
     if rc != 0:
         raise HostError(rc, (L.dissem_last_error() or b"").decode())
     return json.loads(_take(L, out))

@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <stdexcept>
 
 #include "../../include/dissem_host.h"
 #include "../csrc/dissem_engine.h"
@@ -148,66 +149,133 @@ int dissem_plan_json(const char *config_json_text, int mode, uint64_t seed, int 
     return *json_out ? DISSEM_OK : set_error(DISSEM_ENOMEM, "out of memory");
 }
 
+// One message of any kind from its JSON description {"kind":..., fields...}; throws on an unknown kind.
+static MessagePtr msg_from_json(const Json &k) {
+    const Json *kind = k.get("kind");
+    if (!kind) throw std::runtime_error("missing kind");
+    auto geti = [&](const char *key) { const Json *v = k.get(key); return v ? v->as_int() : 0; };
+    if (kind->s == "announce") {
+        auto a = std::make_shared<AnnounceMsg>();
+        a->SrcID = (NodeID)geti("SrcID");
+        if (const Json *ids = k.get("LayerIDs"))
+            for (auto &kv : ids->obj) {
+                LayerMeta meta;
+                if (const Json *v = kv.second.get("Location")) meta.Location = (LayerLocation)v->as_int();
+                if (const Json *v = kv.second.get("LimitRate")) meta.LimitRate = v->as_int();
+                if (const Json *v = kv.second.get("SourceType")) meta.Source = (SourceType)v->as_int();
+                if (const Json *v = kv.second.get("DataSize")) meta.DataSize = v->as_int();
+                a->Layers[(LayerID)strtoul(kv.first.c_str(), nullptr, 10)] = meta;
+            }
+        return a;
+    }
+    if (kind->s == "ack") {
+        auto a = std::make_shared<AckMsg>();
+        a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID"); a->location = (LayerLocation)geti("location");
+        return a;
+    }
+    if (kind->s == "retransmit") {
+        auto a = std::make_shared<RetransmitMsg>();
+        a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID"); a->DestID = (NodeID)geti("DestID");
+        return a;
+    }
+    if (kind->s == "flowRetransmit") {
+        auto a = std::make_shared<FlowRetransmitMsg>();
+        a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID"); a->DestID = (NodeID)geti("DestID");
+        a->DataSize = geti("DataSize"); a->Offset = geti("Offset"); a->Rate = geti("Rate");
+        return a;
+    }
+    if (kind->s == "startup") {
+        auto a = std::make_shared<StartupMsg>();
+        a->SrcID = (NodeID)geti("SrcID");
+        return a;
+    }
+    if (kind->s == "simple") {
+        auto a = std::make_shared<SimpleMsg>();
+        if (const Json *v = k.get("SrcAddr")) a->SrcAddr = v->s;
+        if (const Json *v = k.get("PayloadStr")) a->PayloadStr = v->s;
+        return a;
+    }
+    if (kind->s == "layerHeader") {
+        auto a = std::make_shared<LayerMsg>();
+        a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID");
+        a->Src_.InDevice = true; a->Src_.DataSize = geti("LayerSize"); a->Src_.Offset = geti("Offert");
+        a->TotalSize = geti("TotalSize");
+        return a;
+    }
+    throw std::runtime_error("unknown kind '" + kind->s + "'");
+}
+
+// What a receiver observes of a delivered message
+static Json msg_to_json(const Message &m) {
+    Json d = Json::object();
+    d.set("type", Json::of((int64_t)m.Type()));
+    d.set("src", Json::of(m.Src()));
+    d.set("payload", m.Payload());
+    if (auto *ack = dynamic_cast<const AckMsg *>(&m)) d.set("location_after_decode", Json::of((int64_t)ack->location));
+    return d;
+}
+
 int dissem_msg_roundtrip_json(const char *kind_json, char **wire_out, char **decoded_out) {
     if (!kind_json || !wire_out || !decoded_out) return set_error(DISSEM_EINVAL, "dissem_msg_roundtrip_json: bad arguments");
     try {
-        Json k = Json::parse(kind_json);
-        const Json *kind = k.get("kind");
-        if (!kind) return set_error(DISSEM_EINVAL, "missing kind");
-        auto geti = [&](const char *key) { const Json *v = k.get(key); return v ? v->as_int() : 0; };
-        MessagePtr m;
-        if (kind->s == "announce") {
-            auto a = std::make_shared<AnnounceMsg>();
-            a->SrcID = (NodeID)geti("SrcID");
-            if (const Json *ids = k.get("LayerIDs"))
-                for (auto &kv : ids->obj) {
-                    LayerMeta meta;
-                    if (const Json *v = kv.second.get("Location")) meta.Location = (LayerLocation)v->as_int();
-                    if (const Json *v = kv.second.get("LimitRate")) meta.LimitRate = v->as_int();
-                    if (const Json *v = kv.second.get("SourceType")) meta.Source = (SourceType)v->as_int();
-                    if (const Json *v = kv.second.get("DataSize")) meta.DataSize = v->as_int();
-                    a->Layers[(LayerID)strtoul(kv.first.c_str(), nullptr, 10)] = meta;
-                }
-            m = a;
-        } else if (kind->s == "ack") {
-            auto a = std::make_shared<AckMsg>();
-            a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID"); a->location = (LayerLocation)geti("location");
-            m = a;
-        } else if (kind->s == "retransmit") {
-            auto a = std::make_shared<RetransmitMsg>();
-            a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID"); a->DestID = (NodeID)geti("DestID");
-            m = a;
-        } else if (kind->s == "flowRetransmit") {
-            auto a = std::make_shared<FlowRetransmitMsg>();
-            a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID"); a->DestID = (NodeID)geti("DestID");
-            a->DataSize = geti("DataSize"); a->Offset = geti("Offset"); a->Rate = geti("Rate");
-            m = a;
-        } else if (kind->s == "startup") {
-            auto a = std::make_shared<StartupMsg>();
-            a->SrcID = (NodeID)geti("SrcID");
-            m = a;
-        } else if (kind->s == "simple") {
-            auto a = std::make_shared<SimpleMsg>();
-            if (const Json *v = k.get("SrcAddr")) a->SrcAddr = v->s;
-            if (const Json *v = k.get("PayloadStr")) a->PayloadStr = v->s;
-            m = a;
-        } else if (kind->s == "layerHeader") {
-            auto a = std::make_shared<LayerMsg>();
-            a->SrcID = (NodeID)geti("SrcID"); a->Layer = (LayerID)geti("LayerID");
-            a->Src_.InDevice = true; a->Src_.DataSize = geti("LayerSize"); a->Src_.Offset = geti("Offert");
-            a->TotalSize = geti("TotalSize");
-            m = a;
-        } else return set_error(DISSEM_EINVAL, "unknown kind '%s'", kind->s.c_str());
+        MessagePtr m = msg_from_json(Json::parse(kind_json));
         std::string wire = EncodeMsg(*m);
         MessagePtr back = DecodeMsg(wire);
-        Json d = Json::object();
-        d.set("type", Json::of((int64_t)back->Type()));
-        d.set("src", Json::of(back->Src()));
-        d.set("payload", back->Payload());
-        if (auto *ack = dynamic_cast<AckMsg *>(back.get())) d.set("location_after_decode", Json::of((int64_t)ack->location));
         *wire_out = dup_cstr(wire);
-        *decoded_out = dup_cstr(d.dump());
+        *decoded_out = dup_cstr(msg_to_json(*back).dump());
         return DISSEM_OK;
+    } catch (const std::exception &e) {
+        return set_error(DISSEM_EPARSE, "%s", e.what());
+    }
+}
+
+int dissem_transport_script_json(const char *script_json, char **json_out) {
+    if (!script_json || !json_out) return set_error(DISSEM_EINVAL, "dissem_transport_script_json: bad arguments");
+    try {
+        Json script = Json::parse(script_json);
+        const Json *peers = script.get("peers");
+        const Json *ops = script.get("ops");
+        if (!peers || !ops) return set_error(DISSEM_EINVAL, "script needs \"peers\" and \"ops\"");
+        DeviceFabric fabric(nullptr);                   // control plane only: no device context behind it
+        std::map<NodeID, std::unique_ptr<DeviceTransport>> ts;
+        for (auto &p : peers->arr) ts[(NodeID)p.as_int()].reset(new DeviceTransport(&fabric, (NodeID)p.as_int()));
+        Json results = Json::array();
+        for (auto &op : ops->arr) {
+            const Json *name = op.get("op");
+            auto geti = [&](const char *key) { const Json *v = op.get(key); return v ? v->as_int() : -1; };
+            int rc = DISSEM_EINVAL;
+            if (name && name->s == "send") {
+                auto it = ts.find((NodeID)geti("from"));
+                if (it != ts.end() && op.get("msg")) rc = it->second->Send((NodeID)geti("to"), msg_from_json(*op.get("msg")));
+            } else if (name && name->s == "broadcast") {
+                auto it = ts.find((NodeID)geti("from"));
+                if (it != ts.end() && op.get("msg")) rc = it->second->Broadcast(msg_from_json(*op.get("msg")));
+            } else if (name && name->s == "close") {
+                auto it = ts.find((NodeID)geti("peer"));
+                if (it != ts.end()) rc = it->second->Close();
+            } else if (name && name->s == "pipe") {
+                auto it = ts.find((NodeID)geti("from"));
+                if (it != ts.end()) rc = it->second->RegisterPipe((LayerID)geti("layer"), (NodeID)geti("to"));
+            }
+            results.push(Json::of((int64_t)rc));
+        }
+        // Deliver(): what each peer's consumer would read, in order (channels are closed first so that Pop ends)
+        Json delivered = Json::object();
+        Json addrs = Json::object();
+        for (auto &kv : ts) {
+            addrs.set(std::to_string(kv.first), Json::of(kv.second->GetAddress()));
+            kv.second->Close();
+            Json list = Json::array();
+            MessagePtr m;
+            while (kv.second->Deliver().Pop(&m)) list.push(msg_to_json(*m));
+            delivered.set(std::to_string(kv.first), std::move(list));
+        }
+        Json out = Json::object();
+        out.set("results", std::move(results));
+        out.set("delivered", std::move(delivered));
+        out.set("addresses", std::move(addrs));
+        *json_out = dup_cstr(out.dump());
+        return *json_out ? DISSEM_OK : set_error(DISSEM_ENOMEM, "out of memory");
     } catch (const std::exception &e) {
         return set_error(DISSEM_EPARSE, "%s", e.what());
     }

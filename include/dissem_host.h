@@ -62,6 +62,13 @@ int dissem_run_json(const char *config_json, int mode, const int *node_device, c
  * kind_json: {"kind":"announce|ack|retransmit|flowRetransmit|startup|simple|layerHeader", fields...}. */
 int dissem_msg_roundtrip_json(const char *kind_json, char **wire_out, char **decoded_out);
 
+/* The Transport interface (transport.go:18-25) of the device transport, driven from a script so that the reference's
+ * transport tests (transport_test.go:18-186: send one, send three in order, broadcast) can be replayed without Go.
+ * Control messages need no GPU.  script_json: {"peers":[1,2], "ops":[{"op":"send","from":1,"to":2,"msg":{kind_json}},
+ * {"op":"broadcast","from":1,"msg":{..}}, {"op":"close","peer":2}, {"op":"pipe","from":1,"layer":3,"to":2}]}.
+ * *json_out: {"results":[return code per op], "delivered":{"<peer>":[messages in Deliver() order]}, "addresses":{..}}. */
+int dissem_transport_script_json(const char *script_json, char **json_out);
+
 /* LimitRate pacing: TcpTransport.writeWithLimit (transport.go:407-424) sends a fragment in sub-writes of at most
  * 256 KiB, each after rate.Limiter.WaitN (golang.org/x/time/rate v0.14.0, go.mod:8; burst = 256 KiB, bucket full at
  * the start).  This returns the device-side schedule for the `size` bytes at `layer_off` of a layer: pieces that end on

@@ -391,3 +391,61 @@ def test_plan_optimize_reads_a_disk_layer_once():
     # without disk sources nothing is shifted
     plain, _ = d.plan_optimize([d.Xfer(0, n, 7, 0, 0, 1 << 20, 1 << 20) for n in (1, 2)], [0, 1, 2])
     assert all(d.xfer_round(x) == 0 for x in plain)
+
+
+# ---- the reference's own transport tests (distributor/transport_test.go), replayed on the device transport ----------
+def _simple(text, src="gpu:1"):
+    return {"kind": "simple", "SrcAddr": src, "PayloadStr": text}
+
+
+def test_transport_send_single():
+    """TestTransportSendSingle (transport_test.go:18-68): p1.Send(peer2, msg) is delivered on p2.Deliver()."""
+    r = host.transport_script([1, 2], [{"op": "send", "from": 1, "to": 2, "msg": _simple("hi from peer1")}])
+    assert r["results"] == [0]
+    assert [m["payload"]["PayloadStr"] for m in r["delivered"]["2"]] == ["hi from peer1"]
+    assert r["delivered"]["1"] == [] and r["addresses"] == {"1": "gpu:1", "2": "gpu:2"}
+
+
+def test_transport_send_three_in_order():
+    """TestInmemoryTransportSendThree (transport_test.go:70-138): three messages arrive, equal to what was sent, in order."""
+    texts = ["hi 0", "hi 1", "hi 2"]
+    r = host.transport_script([1, 2], [{"op": "send", "from": 1, "to": 2, "msg": _simple(t)} for t in texts])
+    assert r["results"] == [0, 0, 0]
+    got = r["delivered"]["2"]
+    assert [m["payload"]["PayloadStr"] for m in got] == texts
+    assert all(m["type"] == 7 and m["src"] == "gpu:1" and m["payload"]["SrcAddr"] == "gpu:1" for m in got)
+    # interleaved senders keep their own order (one queue per receiver)
+    ops = [{"op": "send", "from": 1 + (i % 2), "to": 3, "msg": _simple(f"m{i}", src=f"gpu:{1 + i % 2}")} for i in range(10)]
+    got = host.transport_script([1, 2, 3], ops)["delivered"]["3"]
+    assert [m["payload"]["PayloadStr"] for m in got] == [f"m{i}" for i in range(10)]
+
+
+def test_transport_broadcast_single():
+    """TestInmemoryTransportBroadcastSingle (transport_test.go:140-186): Broadcast reaches the other peer — and, as
+    transport.go:290-306 iterates the whole registry, the sender itself."""
+    r = host.transport_script([1, 2, 3], [{"op": "broadcast", "from": 1, "msg": _simple("broadcast value")}])
+    assert r["results"] == [0]
+    for peer in ("1", "2", "3"):
+        assert [m["payload"]["PayloadStr"] for m in r["delivered"][peer]] == ["broadcast value"]
+
+
+def test_transport_contract_edges():
+    """Self-send is legal (SURVEY §8(b)); an unknown destination is an error the caller logs (transport.go:263-265);
+    a closed peer is gone from the registry; RegisterPipe is outside the device transport; control messages keep what
+    the JSON envelope keeps (ackMsg.location is unexported and therefore lost, message.go:62-66)."""
+    ack = {"kind": "ack", "SrcID": 2, "LayerID": 5, "location": 1}
+    r = host.transport_script([1, 2], [
+        {"op": "send", "from": 1, "to": 1, "msg": _simple("to myself")},
+        {"op": "send", "from": 1, "to": 9, "msg": _simple("nobody")},
+        {"op": "send", "from": 2, "to": 1, "msg": ack},
+        {"op": "pipe", "from": 1, "layer": 3, "to": 2},
+        {"op": "close", "peer": 2},
+        {"op": "send", "from": 1, "to": 2, "msg": _simple("too late")},
+    ])
+    assert r["results"] == [0, -4, 0, -8, 0, -4]
+    one = r["delivered"]["1"]
+    assert one[0]["payload"]["PayloadStr"] == "to myself"
+    assert one[1]["type"] == 1 and one[1]["payload"] == {"SrcID": 2, "LayerID": 5} and one[1]["location_after_decode"] == 0
+    assert r["delivered"]["2"] == []
+    with pytest.raises(host.HostError):
+        host.transport_script([1], [{"op": "send", "from": 1, "to": 1, "msg": {"kind": "nonsense"}}])
