@@ -282,3 +282,21 @@ def test_batched_distribution_from_disk_with_fanout(tmp_path):
     for batched in (True, False):
         r = host.run_distribution(text, 0, batched=batched, seed=SEED, timeout_ms=20000, storage=str(tmp_path / str(batched)))
         assert r["verified"] and r["ready_equals_assignment"] and r["layers_checked"] == 7
+
+
+def test_diskspeed_tool(tmp_path):
+    """diskspeed/main.go: `-path file` prints the file size, the time to load it and MiB/s; here the load ends in HBM."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "distributed-llm-dissemination_b200", "diskspeed")
+    if not os.path.exists(exe):
+        pytest.skip("diskspeed not built")
+    assert subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout == "usage: -path [file path]\n"
+    size = STAGE + 12345
+    path = _file_with(tmp_path, 0, 0, o.fill_bytes(o.FILL_PATTERN, 0, size, SEED))
+    r = subprocess.run([exe, "-path", path], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.strip().splitlines()
+    assert lines[0] == f"File size: {size}" and lines[1].startswith("Time to load: ") and lines[2].startswith("Throughput: ")
+    assert float(lines[2].split()[1]) > 0 and lines[2].endswith("MiB/s")
+    bad = subprocess.run([exe, "-path", str(tmp_path / "nope")], capture_output=True, text=True, timeout=60)
+    assert bad.returncode != 0 and "failed to get fileInfo" in bad.stderr
