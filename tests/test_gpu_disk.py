@@ -144,7 +144,7 @@ def test_disk_tier_errors(tmp_path):
         assert np.array_equal(eng.read(1, 3), o.read_disk_section(path, 0, size))
 
 
-@pytest.mark.parametrize("mode,batched", [(0, False), (1, False), (1, True), (3, False), (3, True)])
+@pytest.mark.parametrize("mode,batched", [(0, False), (1, False), (1, True), (2, False), (3, False), (3, True)])
 def test_distribution_from_disk_layers(tmp_path, mode, batched):
     """`-s`: every node's initial layers are files (CreateDiskLayer); the roles send them as DiskLayer sources and
     the receivers end with in-memory copies (assignmentSatisfied wants Location == InmemLayer, node.go:440)."""
@@ -174,10 +174,11 @@ def test_cli_storage_flag(tmp_path):
     if not os.path.exists(exe):
         pytest.skip("CLI not built")
     cfg = os.path.join(root, "tests", "data", "cli_config_4x8.json")
-    r = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", "1", "-s", str(tmp_path), "-v"], capture_output=True, text=True, timeout=180)
-    assert r.returncode == 0, r.stderr
-    assert f"storagePath: {tmp_path}" in r.stdout and "Time to deliver: " in r.stdout
-    assert '"verified":true' in r.stdout
+    for mode, extra in (("1", []), ("2", []), ("3", ["--pace"]), ("0", ["--batched"])):
+        r = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", mode, "-s", str(tmp_path), "-v"] + extra, capture_output=True, text=True, timeout=180)
+        assert r.returncode == 0, (mode, r.stderr)
+        assert f"storagePath: {tmp_path}" in r.stdout and "Time to deliver: " in r.stdout
+        assert '"verified":true' in r.stdout and '"ready_equals_assignment":true' in r.stdout, (mode, r.stdout)
     conf = o.parse_config(open(cfg).read())
     for n in conf.nodes:
         for layer, (sz, _) in n.layers.items():
