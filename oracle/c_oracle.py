@@ -5,7 +5,7 @@ from __future__ import annotations
 import ctypes
 import os
 import subprocess
-from typing import Sequence
+from typing import Optional, Sequence
 
 import numpy as np
 
@@ -31,6 +31,10 @@ def lib() -> ctypes.CDLL:
         _LIB.oracle_tcp_run.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(OracleXfer),
                                         ctypes.c_int, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int,
                                         ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]
+        _LIB.oracle_tcp_run_ex.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(OracleXfer),
+                                           ctypes.c_int, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_char_p),
+                                           ctypes.POINTER(ctypes.c_int64), ctypes.c_int,
+                                           ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]
     return _LIB
 
 
@@ -53,15 +57,25 @@ def checksum(data: np.ndarray, chunk_bytes: int = 256 * 1024) -> np.ndarray:
 
 
 def tcp_run(n_nodes: int, leader: int, xfers: Sequence, src_layers: Sequence[np.ndarray],
-            base_port: int = 18080, verify: bool = True):
+            base_port: int = 18080, verify: bool = True, src_paths: Optional[Sequence[Optional[str]]] = None,
+            rates: Optional[Sequence[int]] = None):
     """Run the transfer list once over loopback TCP.  `src_layers[i]` is the WHOLE source layer of
-    transfer i (uint8 array).  Returns (seconds, bytes_moved)."""
+    transfer i (uint8 array).  `src_paths[i]` (optional) names a file that holds that layer instead (DiskLayer: the
+    sender copies the section out of the file; `src_layers[i]` is then only what verification compares with, and may
+    be None).  `rates[i]` (optional) is the transfer's LimitRate in bytes/s (<= 0: no limiter).
+    Returns (seconds, bytes_moved)."""
     n = len(xfers)
     arr = (OracleXfer * max(n, 1))()
     ptrs = (ctypes.c_void_p * max(n, 1))()
+    paths = (ctypes.c_char_p * max(n, 1))()
+    lims = (ctypes.c_int64 * max(n, 1))()
     for i, x in enumerate(xfers):
         arr[i] = OracleXfer(x.src, x.dst, x.layer, 0, x.off, x.size, x.total)
-        ptrs[i] = src_layers[i].ctypes.data
+        ptrs[i] = src_layers[i].ctypes.data if src_layers[i] is not None else None
+        paths[i] = src_paths[i].encode() if src_paths and src_paths[i] else None
+        lims[i] = int(rates[i]) if rates else 0
+        if ptrs[i] is None and not paths[i]:
+            raise ValueError(f"transfer {i} has neither source bytes nor a source file")
     sec = ctypes.c_double(0.0)
     moved = ctypes.c_int64(0)
     # a port of the block may be taken on a shared box: try a few blocks before giving up
@@ -70,8 +84,8 @@ def tcp_run(n_nodes: int, leader: int, xfers: Sequence, src_layers: Sequence[np.
         port = base_port + attempt * 997
         if port + n_nodes >= 65000:
             port = 20000 + (port % 20000)
-        rc = lib().oracle_tcp_run(n_nodes, leader, port, arr, n, ptrs, int(verify),
-                                  ctypes.byref(sec), ctypes.byref(moved))
+        rc = lib().oracle_tcp_run_ex(n_nodes, leader, port, arr, n, ptrs, paths, lims, int(verify),
+                                     ctypes.byref(sec), ctypes.byref(moved))
         if rc == 0 or rc == -2:
             break
     if rc != 0:

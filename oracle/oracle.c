@@ -14,8 +14,12 @@
  *        transport.go:308-331   JSON envelope {"type":2,"src":"<id>","payload":{SrcID,LayerID,
  *                               LayerSize,TotalSize,Offert}} written first
  *        transport.go:342-345   then raw bytes data[Offset:Offset+DataSize]
- *        transport.go:407-424   in writes of at most 256 KiB (the limiter's burst); the pacing
- *                               of golang.org/x/time/rate v0.14.0 is NOT restated (rate = inf)
+ *        transport.go:407-424   in writes of at most 256 KiB (the limiter's burst); oracle_tcp_run runs without
+ *                               the limiter (rate = inf), oracle_tcp_run_ex restates the token bucket of
+ *                               golang.org/x/time/rate v0.14.0 per transfer (module not under /root/reference;
+ *                               published algorithm; PARITY UNPINNED: no reference test exercises it)
+ *        transport.go:351-367   DiskLayer source (oracle_tcp_run_ex with a file): section of the file copied out
+ *                               through a 32 KiB buffer (io.Copy's generic path), no limiter
  *        transport.go:97-103    receiver: streaming JSON decode of the envelope
  *        transport.go:201-207   fresh zeroed buffer of LayerSize, then read-full
  *        node.go:1354-1384      store, then ackMsg to the leader over the persistent control
@@ -29,6 +33,7 @@
 #define _GNU_SOURCE
 #include <arpa/inet.h>
 #include <errno.h>
+#include <fcntl.h>
 #include <netinet/in.h>
 #include <netinet/tcp.h>
 #include <pthread.h>
@@ -124,7 +129,9 @@ struct run_s {
     int n_nodes, leader, base_port;
     const oracle_xfer *xf;
     int n_xf;
-    const uint8_t *const *src_base;      /* per transfer: base pointer of the SOURCE layer */
+    const uint8_t *const *src_base;      /* per transfer: base pointer of the SOURCE layer (NULL: read it from src_path) */
+    const char *const *src_path;         /* per transfer: file holding the source layer (DiskLayer), or NULL (may be NULL itself) */
+    const int64_t *rate;                 /* per transfer: LimitRate in bytes/s, <= 0 = no limiter (may be NULL) */
     listener_t *lis;
     pthread_mutex_t mu;
     pthread_cond_t cv;
@@ -337,12 +344,51 @@ static void *send_main(void *arg) {
                      "\"TotalSize\":%lld,\"Offert\":%lld}}",
                      x->src, x->src, x->layer, (long long)x->size, (long long)x->total, (long long)x->off);
     int rc = write_full(fd, hdr, (size_t)n);
-    const uint8_t *p = r->src_base[sa->i] + x->off;
-    int64_t left = x->size;
-    while (rc == 0 && left > 0) {
-        int64_t k = left < ORACLE_CHUNK ? left : ORACLE_CHUNK;   /* min(len(data), limiter.Burst()) */
-        rc = write_full(fd, p, (size_t)k);
-        p += k; left -= k;
+    const char *path = r->src_path ? r->src_path[sa->i] : NULL;
+    if (path) {
+        /* DiskLayer, transport.go:351-367: io.Copy(conn, io.NewSectionReader(f, Offset, DataSize)).  A SectionReader is
+         * not an *os.File, so TCPConn.ReadFrom falls back to the generic copy loop: read into a 32 KiB buffer, write it
+         * out (the comment at :362 hopes for sendfile; the code path is this one).  No limiter on this branch. */
+        int ffd = open(path, O_RDONLY);
+        if (ffd < 0) rc = -1;
+        static __thread uint8_t cp[32 * 1024];
+        int64_t pos = x->off, left = x->size;
+        while (rc == 0 && left > 0) {
+            ssize_t k = pread(ffd, cp, (size_t)(left < (int64_t)sizeof cp ? left : (int64_t)sizeof cp), (off_t)pos);
+            if (k < 0 && errno == EINTR) continue;
+            if (k <= 0) { rc = -1; break; }
+            rc = write_full(fd, cp, (size_t)k);
+            pos += k; left -= k;
+        }
+        if (ffd >= 0) close(ffd);
+    } else {
+        /* writeWithLimit, transport.go:407-424: limiter := rate.NewLimiter(rate.Limit(limitRate), 256 KiB); per write
+         * n = min(len(data), burst); limiter.WaitN(n).  golang.org/x/time/rate v0.14.0 (go.mod:8), restated: the bucket
+         * starts full; reserveN advances it by elapsed*limit (capped at burst), takes n, and a negative balance waits
+         * -tokens/limit seconds.  rate <= 0 here means "no limiter" (with limit 0 the reference never finishes). */
+        const double limit = (r->rate && r->rate[sa->i] > 0) ? (double)r->rate[sa->i] : 0.0;
+        double tokens = (double)ORACLE_CHUNK, last = now_s();
+        const uint8_t *p = r->src_base[sa->i] + x->off;
+        int64_t left = x->size;
+        while (rc == 0 && left > 0) {
+            int64_t k = left < ORACLE_CHUNK ? left : ORACLE_CHUNK;   /* min(len(data), limiter.Burst()) */
+            if (limit > 0.0) {
+                double now = now_s();
+                tokens += (now - last) * limit;
+                if (tokens > (double)ORACLE_CHUNK) tokens = (double)ORACLE_CHUNK;
+                tokens -= (double)k;
+                last = now;
+                if (tokens < 0.0) {
+                    double wait = -tokens / limit;
+                    struct timespec ts;
+                    ts.tv_sec = (time_t)wait;
+                    ts.tv_nsec = (long)((wait - (double)ts.tv_sec) * 1e9);
+                    while (nanosleep(&ts, &ts) != 0 && errno == EINTR) {}
+                }
+            }
+            rc = write_full(fd, p, (size_t)k);
+            p += k; left -= k;
+        }
     }
     close(fd);                                                   /* defer conn.Close(), :273 */
     if (rc < 0) fail(r);
@@ -355,13 +401,26 @@ static void *send_main(void *arg) {
  * csum_out (may be NULL) receives, per transfer, A and B of chunk 0 of the destination layer as a spot
  * check.  max_inflight > 0 bounds concurrently running sender threads (0 = one per transfer, as the
  * reference's goroutine-per-send). */
+int oracle_tcp_run_ex(int n_nodes, int leader, int base_port, const oracle_xfer *xf, int n_xf,
+                      const uint8_t *const *src_base, const char *const *src_path, const int64_t *rate, int verify,
+                      double *seconds, int64_t *bytes_moved);
+
 int oracle_tcp_run(int n_nodes, int leader, int base_port, const oracle_xfer *xf, int n_xf,
                    const uint8_t *const *src_base, int verify, double *seconds, int64_t *bytes_moved) {
+    return oracle_tcp_run_ex(n_nodes, leader, base_port, xf, n_xf, src_base, NULL, NULL, verify, seconds, bytes_moved);
+}
+
+/* The same with, per transfer, an optional source FILE (the DiskLayer branch of sendLayerMsg) and an optional LimitRate
+ * (writeWithLimit's token bucket).  With a file source, src_base[i] may still be given: it is then what verification
+ * compares the destination with (the expected contents of the file). */
+int oracle_tcp_run_ex(int n_nodes, int leader, int base_port, const oracle_xfer *xf, int n_xf,
+                      const uint8_t *const *src_base, const char *const *src_path, const int64_t *rate, int verify,
+                      double *seconds, int64_t *bytes_moved) {
     if (n_nodes <= 0 || n_nodes > 64 || n_xf < 0) return -1;
     run_t r;
     memset(&r, 0, sizeof r);
     r.n_nodes = n_nodes; r.leader = leader; r.base_port = base_port;
-    r.xf = xf; r.n_xf = n_xf; r.src_base = src_base;
+    r.xf = xf; r.n_xf = n_xf; r.src_base = src_base; r.src_path = src_path; r.rate = rate;
     pthread_mutex_init(&r.mu, NULL);
     pthread_cond_init(&r.cv, NULL);
     for (int i = 0; i < 64; ++i) { r.ctrl_fd[i] = -1; pthread_mutex_init(&r.ctrl_mu[i], NULL); }
@@ -421,9 +480,8 @@ int oracle_tcp_run(int n_nodes, int leader, int base_port, const oracle_xfer *xf
                     recv_layer_t *rl = NULL;
                     for (int j = 0; j < r.n_rl; ++j)
                         if (r.rl_node[j] == xf[i].dst && r.rl[j].layer == xf[i].layer) rl = &r.rl[j];
-                    if (!rl || !rl->buf || rl->got != rl->total ||
-                        memcmp(rl->buf + xf[i].off, src_base[i] + xf[i].off, (size_t)xf[i].size) != 0)
-                        rc = -2;
+                    if (!rl || !rl->buf || rl->got != rl->total) { rc = -2; break; }
+                    if (src_base[i] && memcmp(rl->buf + xf[i].off, src_base[i] + xf[i].off, (size_t)xf[i].size) != 0) rc = -2;
                 }
             }
         }

@@ -203,3 +203,22 @@ def test_disk_layer_restatement(tmp_path):
     assert np.array_equal(o.read_disk_section(p, 0, 5000), marked)
     assert np.array_equal(o.read_disk_section(p, 123, 1000), marked[123:1123])
     assert o.create_disk_layer(str(tmp_path), 3, 12, -4) and o.read_disk_section(o.disk_layer_path(str(tmp_path), 3, 12), 0, 10).size == 0
+
+
+def test_tcp_restatement_disk_source_and_limit_rate(tmp_path):
+    """The loopback-TCP restatement with (a) a DiskLayer source (sendLayerMsg copies the file section, transport.go:351-367)
+    and (b) writeWithLimit's token bucket (transport.go:407-424): the paced send takes what limiter_write_times says."""
+    size = 3 * 262144 + 999
+    a = o.fill_bytes(o.FILL_PATTERN, 1, size, 7)
+    b = o.fill_bytes(o.FILL_PATTERN, 2, size, 7)
+    path = o.create_disk_layer(str(tmp_path), 0, 1, size, contents=a)
+    xs = [o.Xfer(0, 1, 1, 0, 1000, size), o.Xfer(0, 1, 1, 1000, size - 1000, size), o.Xfer(0, 2, 2, 0, size, size)]
+    secs, moved = co.tcp_run(3, 0, xs, [a, None, b], base_port=24100, src_paths=[path, path, None])
+    assert moved == 2 * size
+    with pytest.raises(RuntimeError):                      # the file does not hold what the caller expects: verification fails
+        co.tcp_run(3, 0, [o.Xfer(0, 1, 1, 0, size, size)], [b], base_port=24200, src_paths=[path])
+    rate = 20_000_000
+    want_s = o.limiter_write_times(size, rate)[-1][0] / 1e9
+    fast, _ = co.tcp_run(3, 0, xs[2:], [b], base_port=24300)
+    paced, _ = co.tcp_run(3, 0, xs[2:], [b], base_port=24400, rates=[rate])
+    assert want_s <= paced < want_s + 0.25 and fast < paced
