@@ -92,3 +92,51 @@ def test_mode3_random_configs(text, scale, flags):
         # every fragment list tiles what it delivers, and rates are dataSize * ticks-per-second / t (node.go:1281)
         for x in got["xfers"]:
             assert x[6] == (x[4] * scale // t if t > 0 else 0)
+
+
+def test_malformed_configs_are_rejected_not_crashed_on():
+    """Mutated and truncated configurations: every call either plans or returns an error code; the library (which a Go
+    process would have loaded) never aborts or hangs.  The reference ignores JSON errors (cmd/config.go:58-59)."""
+    import random
+    base = [o.config_readme(), o.config_ring_fixture(4, 5), o.config_conf_json(), o.config_stage_ring(4, 8, 1000)]
+    rng = random.Random(1)
+    junk = ['', '{', '}', '"', ':', ',', '[', ']', '-', '9' * 25, 'null', 'true', '1e999', '\\', '\\u12', '\x00']
+    weird = [None, -1, 2**63, 2**64, 1.5, "x", [], {}, True, -2**63]
+
+    def mutate(x):
+        if isinstance(x, dict):
+            for key in list(x):
+                r = rng.random()
+                if r < 0.05:
+                    del x[key]
+                elif r < 0.10:
+                    x[key] = rng.choice(weird)
+                else:
+                    mutate(x[key])
+        elif isinstance(x, list):
+            for v in x:
+                mutate(v)
+
+    planned = rejected = 0
+    for it in range(700):
+        t = rng.choice(base)
+        k = rng.randrange(4)
+        if k == 0:
+            i = rng.randrange(len(t))
+            t = t[:i] + rng.choice(junk) + t[i + rng.randrange(3):]
+        elif k == 1:
+            t = t[:rng.randrange(len(t))]
+        elif k == 2:
+            obj = json.loads(t)
+            mutate(obj)
+            t = json.dumps(obj)
+        else:
+            t = ''.join(rng.choice('{}[]":,0123456789.eE-+ \n\tabcNodesId') for _ in range(rng.randrange(60)))
+        for mode in (0, 1, 2, 3):
+            try:
+                d.plan(t, mode, seed=it, time_scale=rng.choice([1, 1000]))
+                planned += 1
+            except d.DissemError as e:
+                assert e.code in (-1, -9, -10)
+                rejected += 1
+    assert planned > 200 and rejected > 200
