@@ -140,3 +140,49 @@ def test_malformed_configs_are_rejected_not_crashed_on():
                 assert e.code in (-1, -9, -10)
                 rejected += 1
     assert planned > 200 and rejected > 200
+
+
+@st.composite
+def transfer_lists(draw):
+    n_nodes = draw(st.integers(2, 8))
+    xs = []
+    for layer in range(draw(st.integers(1, 5))):
+        total = draw(st.sampled_from([1, 4096, 262144, 300_001, 9 << 20, 70 << 20, 300 << 20]))
+        src = draw(st.integers(0, n_nodes - 1))
+        dsts = draw(st.lists(st.integers(0, n_nodes - 1).filter(lambda n: n != src), min_size=1, max_size=4, unique=True))
+        whole = draw(st.booleans())
+        off = 0 if whole else draw(st.integers(0, total - 1))
+        size = total if whole else draw(st.integers(1, total - off))
+        flags = d.XFER_FILE if draw(st.integers(0, 4)) == 0 else 0
+        xs += [d.Xfer(src, dst, layer, flags, off, size, total) for dst in dsts]
+    gpus = [draw(st.integers(0, 3)) for _ in range(n_nodes)]
+    return xs, gpus
+
+
+@settings(max_examples=150, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow])
+@given(transfer_lists(), st.integers(1, 9))
+def test_relay_and_optimize_conserve_every_byte(case, pieces):
+    """Whatever dissem_plan_relay / dissem_plan_optimize do to a plan, every destination still receives exactly the bytes
+    it was to receive, once; and whoever forwards a range has received it in an earlier round (or is the original source)."""
+    xs, gpus = case
+    want = {}
+    for x in xs:
+        want.setdefault((x.dst_node, x.layer), []).append((x.off, x.off + x.size))
+    for plan in (d.plan_relay(xs, pieces), d.plan_optimize(xs, gpus)[0]):
+        got = {}
+        for y in plan:
+            got.setdefault((y.dst_node, y.layer), []).append((y.off, y.off + y.size, d.xfer_round(y), y.src_node, y.flags))
+        assert set(got) == set(want)
+        for key, ranges in got.items():
+            ranges.sort()
+            (a0, b0), = want[key]
+            assert ranges[0][0] == a0 and ranges[-1][1] == b0
+            assert all(r1[1] == r2[0] for r1, r2 in zip(ranges[:-1], ranges[1:]))      # tiles, no gap, no overlap
+        orig_src = {x.layer: x.src_node for x in xs}
+        for y in plan:
+            if y.src_node == orig_src[y.layer]:
+                continue
+            # a forwarder: it must itself receive [off, off+size) of this layer in an earlier round
+            feeds = [r for r in got[(y.src_node, y.layer)] if r[0] <= y.off and y.off + y.size <= r[1]]
+            assert feeds and all(r[2] < d.xfer_round(y) or (r[4] & d.XFER_FILE) for r in feeds)
+            assert not y.flags & d.XFER_FILE
