@@ -114,10 +114,14 @@ func (t *DeviceTransport) Send(destID NodeID, message Message) error {
 
 func (t *DeviceTransport) RegisterPipe(LayerID, NodeID) error { return fmt.Errorf("pipes are not supported") }
 func (t *DeviceTransport) Broadcast(m Message) error {
-	t.fabric.mu.RLock()
-	defer t.fabric.mu.RUnlock()
+	t.fabric.mu.RLock() // ids are copied first, as transport.go:290-297 does: Send takes the lock itself
+	ids := make([]NodeID, 0, len(t.fabric.peers))
 	for id := range t.fabric.peers {
-		_ = t.Send(id, m)
+		ids = append(ids, id)
+	}
+	t.fabric.mu.RUnlock()
+	for _, id := range ids {
+		_ = t.Send(id, m) // errors are logged and dropped, transport.go:299-303
 	}
 	return nil
 }
