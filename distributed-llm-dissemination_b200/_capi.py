@@ -84,6 +84,7 @@ def load_library() -> ctypes.CDLL:
         "dissem_schedule_free": (c.c_int, [P, i64]),
         "dissem_schedule_info": (c.c_int, [P, i64, c.POINTER(i64), c.POINTER(c.c_int), c.POINTER(i64)]),
         "dissem_plan_directions": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int]),
+        "dissem_plan_align": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int)]),
         "dissem_plan_relay": (c.c_int, [c.POINTER(Xfer), c.c_int, c.c_int, c.POINTER(c.POINTER(Xfer)), c.POINTER(c.c_int)]),
         "dissem_plan_optimize": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.POINTER(Xfer)),
                                            c.POINTER(c.c_int), c.POINTER(c.c_int)]),
@@ -91,6 +92,8 @@ def load_library() -> ctypes.CDLL:
         "dissem_wait": (c.c_int, [P, i64, c.POINTER(c.c_double)]),
         "dissem_wait_detail": (c.c_int, [P, i64, c.POINTER(c.c_double), c.POINTER(c.c_double)]),
         "dissem_poll": (c.c_int, [P, i64, c.POINTER(c.c_int)]),
+        "dissem_ticket_release": (c.c_int, [P, i64]),
+        "dissem_layers_checksums": (c.c_int, [P, c.POINTER(c.c_int), c.POINTER(c.c_int), c.c_int, P, i64]),
         "dissem_layer_checksums": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
         "dissem_layer_verify": (c.c_int, [P, c.c_int, c.c_int, P, i64]),
         "dissem_layer_received": (c.c_int, [P, c.c_int, c.c_int, c.POINTER(i64)]),
@@ -141,6 +144,14 @@ def plan_directions(xfers: List["Xfer"], gpu_of_node: Sequence[int]) -> List["Xf
     g = (ctypes.c_int * len(gpu_of_node))(*gpu_of_node)
     _check(lib().dissem_plan_directions(arr, len(xfers), g, len(gpu_of_node)))
     return [Xfer(a.src_node, a.dst_node, a.layer, a.flags, a.off, a.size, a.total) for a in arr[:len(xfers)]]
+
+
+def plan_align(xfers: List["Xfer"]) -> List["Xfer"]:
+    """dissem_plan_align: fragment cuts moved down to checksum-chunk boundaries (empty fragments dropped)."""
+    arr = make_xfers(xfers)
+    m = ctypes.c_int()
+    _check(lib().dissem_plan_align(arr, len(xfers), ctypes.byref(m)))
+    return [Xfer(a.src_node, a.dst_node, a.layer, a.flags, a.off, a.size, a.total) for a in arr[:m.value]]
 
 
 def xfer_round(x: "Xfer") -> int:
@@ -385,6 +396,23 @@ class Engine:
         out = np.zeros((n, 2), dtype=np.uint64)
         _check(lib().dissem_layer_checksums(self._ctx, node, layer, out.ctypes.data, n))
         return out
+
+    def checksums_many(self, pairs: Sequence) -> List[np.ndarray]:
+        """dissem_layers_checksums: the fused tables of several local (node, layer) pairs with one read-back per GPU."""
+        pairs = list(pairs)
+        counts = [self._n_chunks(n, l) for (n, l) in pairs]
+        out = np.zeros((sum(counts), 2), dtype=np.uint64)
+        nodes = (ctypes.c_int * max(len(pairs), 1))(*[n for (n, _l) in pairs])
+        layers = (ctypes.c_int * max(len(pairs), 1))(*[l for (_n, l) in pairs])
+        _check(lib().dissem_layers_checksums(self._ctx, nodes, layers, len(pairs), out.ctypes.data, sum(counts)))
+        res, pos = [], 0
+        for c in counts:
+            res.append(out[pos:pos + c])
+            pos += c
+        return res
+
+    def release(self, ticket: int):
+        _check(lib().dissem_ticket_release(self._ctx, ticket))
 
     def verify(self, node: int, layer: int) -> np.ndarray:
         n = self._n_chunks(node, layer)

@@ -92,8 +92,19 @@ struct DeviceState {
     XferDesc *desc_pool = nullptr;
     std::vector<int> free_slots;
     StageRing ring;
+    // Recorded after every copy kernel this engine enqueues on `stream`.  A launch whose zeroing phase may wipe a
+    // checksum entry that ANOTHER GPU's previous launch is still adding into waits for it first (launch_sched).
+    cudaEvent_t last_end = nullptr;
+    // Read-back side (verify pass, checksum tables, layer reads): its own stream, so that a reader never queues behind
+    // transfers other threads enqueue meanwhile, and a scratch arena (device + pinned host) allocated at dissem_init, so
+    // that no call on this path allocates or frees device memory.  arena_mu serialises the arena's users per GPU.
+    cudaStream_t rd_stream = nullptr;
+    uint8_t *arena_dev = nullptr, *arena_host = nullptr;
+    size_t arena_bytes = 0;
+    std::shared_ptr<std::mutex> arena_mu = std::make_shared<std::mutex>();
     std::shared_ptr<std::mutex> ring_mu = std::make_shared<std::mutex>();   // one file transfer streams through a ring at a time
 };
+constexpr size_t kArenaBytes = 2u << 20;      // verify scratch: descriptor + table of 128 Ki chunks (a 32 GiB layer)
 constexpr int kPoolSlots = 256;
 constexpr int kSlotDescs = 16;
 
@@ -106,12 +117,21 @@ struct SchedPart {
     int n_descs = 0;
     long long total_units = 0;
     int64_t bytes = 0;
+    // (node, layer) of local buffers this part reads or writes that live on ANOTHER GPU: their `ready` events are
+    // waited for before the part's kernels start
+    std::vector<std::pair<int, int>> touch;
+    // (node, layer) of every local destination buffer this part writes: remembered in the buffer (LayerBuf::writers) so
+    // that a later read of it waits for exactly the streams that may still be writing
+    std::vector<std::pair<int, int>> writes;
 };
 
 struct Sched {
     std::vector<SchedPart> parts;
     int unit_shift = kChunkShift;
     int64_t units = 0, bytes = 0;
+    // some checksum entry that this schedule zeroes (an owned, partially covered chunk) is added into by kernels of
+    // several GPUs: a relaunch must not zero it while another GPU's previous launch is still running
+    bool cross_dev_shared = false;
 };
 
 struct TicketPart {
@@ -171,6 +191,23 @@ static int local_dev(dissem_ctx *ctx, int node, DeviceState **out) {
     if (slot < 0) return set_error(DISSEM_EINVAL, "node %d is not local to this process", node);
     *out = &ctx->devs[slot];
     return 0;
+}
+
+// Record `lb.ready` on the owner's stream (ds is current).  Called after the owner enqueued something that writes the
+// buffer; kernels of other GPUs' streams wait for the event (launch_sched), the owner's own stream is ordered anyway.
+static cudaError_t mark_ready(LayerBuf &lb, DeviceState &ds) {
+    if (!lb.ready) {
+        cudaEvent_t ev = nullptr;
+        cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+        lb.ready = ev;
+    }
+    return cudaEventRecord(static_cast<cudaEvent_t>(lb.ready), ds.stream);
+}
+
+static void drop_ready(LayerBuf &lb) {
+    if (lb.ready) cudaEventDestroy(static_cast<cudaEvent_t>(lb.ready));
+    lb.ready = nullptr;
 }
 
 static void free_sched(dissem_ctx *ctx, Sched &s) {
@@ -248,6 +285,7 @@ struct CompileItem {
     dissem_xfer x;
     McObject *mc = nullptr;      // set: one multicast stream standing for n_dsts transfers of the same bytes
     int n_dsts = 1;
+    std::vector<int> mc_dsts;    // the destination nodes of a multicast stream
 };
 
 static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched *out) {
@@ -343,6 +381,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                 it.x = x;
                 it.mc = mc;
                 it.n_dsts = (int)g.members.size();
+                it.mc_dsts = dsts;
                 by_dev[sslot].push_back(it);
                 for (int m : g.members) used[m] = 1;
                 ctx->mcast_groups_compiled++;
@@ -377,11 +416,24 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         long long units = 0;
         int64_t bytes = 0;
         bool any_host_src = false;
+        std::vector<std::pair<int, int>> touch, writes;
+        auto written = [&](int node, int layer) {
+            if (ctx->node_dev_slot[node] < 0) return;                       // an imported buffer: its own process reads it
+            auto key = std::make_pair(node, layer);
+            if (std::find(writes.begin(), writes.end(), key) == writes.end()) writes.push_back(key);
+        };
+        auto touches = [&](int node, int layer, const LayerBuf *lb) {
+            // a local buffer of another GPU: its owner's stream may still be zeroing / filling / uploading it
+            if (lb->imported || lb->host || ctx->node_dev_slot[node] < 0 || ctx->node_dev_slot[node] == (int)slot) return;
+            auto key = std::make_pair(node, layer);
+            if (std::find(touch.begin(), touch.end(), key) == touch.end()) touch.push_back(key);
+        };
         for (auto &it : by_dev[slot]) {
             const dissem_xfer &x = it.x;
             LayerBuf *src = nullptr, *dst = nullptr;
             int rc = find_layer(ctx, x.src_node, x.layer, &src);
             if (rc) return rc;
+            touches(x.src_node, x.layer, src);
             XferDesc d;
             memset(&d, 0, sizeof d);
             d.src = src->base;
@@ -395,6 +447,12 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                 d.csum = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off() + 256);
                 d.received = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off());
                 d.flags = kFlagMulticast;
+                for (int dn : it.mc_dsts) {
+                    LayerBuf *ml = nullptr;
+                    if (find_layer(ctx, dn, x.layer, &ml) == 0) touches(dn, x.layer, ml);
+                    written(dn, x.layer);
+                }
+                written(x.src_node, x.layer);          // the source's own copy is a member of the object
             } else {
                 rc = find_layer(ctx, x.dst_node, x.layer, &dst);
                 if (rc) return rc;
@@ -407,6 +465,8 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                 d.csum = dst->csum();
                 d.received = dst->received();
                 d.flags = 0;
+                touches(x.dst_node, x.layer, dst);
+                written(x.dst_node, x.layer);
             }
             units += units_of(x.off, x.size, out->unit_shift);
             bytes += x.size * (int64_t)it.n_dsts;
@@ -436,6 +496,8 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         part.n_descs = (int)descs.size();
         part.total_units = units;
         part.bytes = bytes;
+        part.touch = std::move(touch);
+        part.writes = std::move(writes);
         out->parts.push_back(part);
         part_descs.push_back(std::move(descs));
         out->units += units;
@@ -450,7 +512,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
     // also receives bytes from other submissions (one Transport.Send per fragment): it is left alone, its entry was
     // zeroed when the destination buffer was allocated or reset.
     {
-        struct Owner { int round; long long off; size_t part, desc; int flag; long long covered, length; };
+        struct Owner { int round; long long off; size_t part, desc; int flag; long long covered, length; int first_slot; bool multi_slot; };
         std::map<std::pair<const void *, long long>, Owner> owners;
         for (size_t pi = 0; pi < part_descs.size(); ++pi)
             for (size_t di = 0; di < part_descs[pi].size(); ++di) {
@@ -465,9 +527,10 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                     auto key = std::make_pair((const void *)d.csum, c);
                     auto it = owners.find(key);
                     if (it == owners.end()) {
-                        owners[key] = Owner{out->parts[pi].round, d.off, pi, di, flag, cov, c1 - c0};
+                        owners[key] = Owner{out->parts[pi].round, d.off, pi, di, flag, cov, c1 - c0, out->parts[pi].dev_slot, false};
                     } else {
                         it->second.covered += cov;
+                        if (out->parts[pi].dev_slot != it->second.first_slot) it->second.multi_slot = true;
                         if (std::make_pair(out->parts[pi].round, (long long)d.off) < std::make_pair(it->second.round, it->second.off)) {
                             it->second.round = out->parts[pi].round;
                             it->second.off = d.off;
@@ -481,7 +544,10 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                 if (ct != ch && end < chunk_end(ct)) consider(ct, kFlagZeroTail);
             }
         for (auto &kv : owners)
-            if (kv.second.covered == kv.second.length) part_descs[kv.second.part][kv.second.desc].flags |= kv.second.flag;
+            if (kv.second.covered == kv.second.length) {
+                part_descs[kv.second.part][kv.second.desc].flags |= kv.second.flag;
+                if (kv.second.multi_slot) out->cross_dev_shared = true;
+            }
     }
     for (size_t pi = 0; pi < out->parts.size(); ++pi) {
         SchedPart &part = out->parts[pi];
@@ -527,6 +593,18 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
             DeviceState &ds = ctx->devs[p.dev_slot];
             CUDA_TRY(cudaSetDevice(ds.dev));
             for (cudaEvent_t ev : prev_round) CUDA_TRY(cudaStreamWaitEvent(ds.stream, ev, 0));
+            // buffers of other GPUs this part touches: wait until their owners' streams have finished writing them
+            // (trailer zeroing at alloc / reset, fill, upload) -- streams of different GPUs are not ordered otherwise
+            for (auto &nl : p.touch) {
+                auto li = ctx->layers[nl.first].find(nl.second);
+                if (li != ctx->layers[nl.first].end() && li->second.ready)
+                    CUDA_TRY(cudaStreamWaitEvent(ds.stream, static_cast<cudaEvent_t>(li->second.ready), 0));
+            }
+            // a relaunch that re-zeroes a checksum entry shared with kernels of other GPUs must not overtake those GPUs'
+            // previous launch (whose partial sums would land after the zeroing)
+            if (s.cross_dev_shared && i == 0)
+                for (auto &other : ctx->devs)
+                    if (other.dev != ds.dev && other.last_end) CUDA_TRY(cudaStreamWaitEvent(ds.stream, other.last_end, 0));
             TicketPart tp;
             tp.dev_slot = p.dev_slot;
             tp.start = tp.mid = tp.end = nullptr;
@@ -548,9 +626,14 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
             CUDA_TRY(cudaSetDevice(ds.dev));
             for (size_t m = i; m < j; ++m)
                 if (m != k) CUDA_TRY(cudaStreamWaitEvent(ds.stream, t->parts[first_tp + (m - i)].mid, 0));
+            for (auto &nl : p.writes) {
+                auto li = ctx->layers[nl.first].find(nl.second);
+                if (li != ctx->layers[nl.first].end()) li->second.writers |= 1ull << (p.dev_slot & 63);
+            }
             LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, p.host_src ? 0 : (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
             CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
             CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
+            if (ds.last_end) CUDA_TRY(cudaEventRecord(ds.last_end, ds.stream));
             this_round.push_back(tp.end);
         }
         prev_round.swap(this_round);
@@ -639,6 +722,7 @@ struct FileJob {
     uint8_t *dst = nullptr;
     unsigned long long *csum = nullptr, *received = nullptr;
     TicketPart tp{-1, nullptr, nullptr, nullptr};
+    cudaEvent_t dst_ready = nullptr;  // set when the destination buffer lives on another GPU than the one that streams the file
     bool owns_fd = false;             // file.fd is a dup() made for this transfer; dissem_schedule_submit closes it
 };
 
@@ -669,6 +753,8 @@ static int prepare_file_job(dissem_ctx *ctx, const dissem_xfer &x, FileJob *job)
     job->dst = dst->base;
     job->csum = dst->csum();
     job->received = dst->received();
+    if (!dst->imported && ctx->node_dev_slot[x.dst_node] != job->dev_slot) job->dst_ready = static_cast<cudaEvent_t>(dst->ready);
+    dst->writers |= 1ull << (job->dev_slot & 63);
     DeviceState &ds = ctx->devs[job->dev_slot];
     CUDA_TRY(cudaSetDevice(ds.dev));
     job->tp.dev_slot = job->dev_slot;
@@ -689,6 +775,7 @@ static int stream_from_file(dissem_ctx *ctx, FileJob &job, const LaunchCfg &cfg_
     if (rc) return rc;
     StageRing &r = ds.ring;
     CUDA_TRY(cudaSetDevice(ds.dev));
+    if (job.dst_ready) CUDA_TRY(cudaStreamWaitEvent(ds.stream, job.dst_ready, 0));   // the owner may still be zeroing its trailer
     CUDA_TRY(cudaEventRecord(job.tp.start, ds.stream));
     CUDA_TRY(cudaEventRecord(job.tp.mid, ds.stream));
     const dissem_xfer &x = job.x;
@@ -734,6 +821,7 @@ static int stream_from_file(dissem_ctx *ctx, FileJob &job, const LaunchCfg &cfg_
         pos = piece_end;
     }
     CUDA_TRY(cudaEventRecord(job.tp.end, ds.stream));
+    if (ds.last_end) CUDA_TRY(cudaEventRecord(ds.last_end, ds.stream));
     return 0;
 }
 
@@ -787,6 +875,11 @@ int dissem_init(int n_nodes, const int *device_of_node, dissem_ctx **out) {
             CUDA_TRY(cudaMemset(ds.counters, 0, sizeof(SchedCounters)));
             CUDA_TRY(cudaMalloc(&ds.desc_pool, (size_t)kPoolSlots * kSlotDescs * sizeof(XferDesc)));
             for (int sl = kPoolSlots - 1; sl >= 0; --sl) ds.free_slots.push_back(sl);
+            CUDA_TRY(cudaEventCreateWithFlags(&ds.last_end, cudaEventDisableTiming));
+            CUDA_TRY(cudaStreamCreateWithFlags(&ds.rd_stream, cudaStreamNonBlocking));
+            CUDA_TRY(cudaMalloc(&ds.arena_dev, kArenaBytes));
+            CUDA_TRY(cudaHostAlloc((void **)&ds.arena_host, kArenaBytes, cudaHostAllocPortable));
+            ds.arena_bytes = kArenaBytes;
             CUDA_TRY(warm_kernels());
             ctx->devs.push_back(ds);
             slot = (int)ctx->devs.size() - 1;
@@ -828,6 +921,7 @@ int dissem_close(dissem_ctx *ctx) {
         for (int n = 0; n < ctx->n_nodes; ++n)
             for (auto &kv : ctx->layers[n]) {
                 LayerBuf &lb = kv.second;
+                drop_ready(lb);
                 if (lb.host) continue;
                 if (lb.vmm) vmm_free(&lb.blk);
                 else if (lb.imported) cudaIpcCloseMemHandle(lb.base);
@@ -852,6 +946,10 @@ int dissem_close(dissem_ctx *ctx) {
             if (ds.ring.d_descs) cudaFree(ds.ring.d_descs);
             cudaFree(ds.counters);
             cudaFree(ds.desc_pool);
+            if (ds.last_end) cudaEventDestroy(ds.last_end);
+            if (ds.arena_dev) cudaFree(ds.arena_dev);
+            if (ds.arena_host) cudaFreeHost(ds.arena_host);
+            if (ds.rd_stream) cudaStreamDestroy(ds.rd_stream);
             cudaStreamDestroy(ds.stream);
         }
     }
@@ -898,6 +996,7 @@ int dissem_layer_alloc(dissem_ctx *ctx, int node, int layer, int64_t size) {
         }
     }
     CUDA_TRY(cudaMemsetAsync(lb.base + lb.trailer_off(), 0, (size_t)lb.trailer_bytes(), ds->stream));
+    CUDA_TRY(mark_ready(lb, *ds));
     ctx->layers[node][layer] = lb;
     return DISSEM_OK;
 }
@@ -943,6 +1042,7 @@ int dissem_layer_free(dissem_ctx *ctx, int node, int layer) {
             it = ctx->mcasts.erase(it);
         } else ++it;
     }
+    drop_ready(*lb);
     if (lb->host) { /* caller-owned memory: nothing to release */ }
     else if (lb->vmm) vmm_free(&lb->blk);                       // owned or imported through a file descriptor
     else if (lb->imported) CUDA_TRY(cudaIpcCloseMemHandle(lb->base));
@@ -984,6 +1084,7 @@ int dissem_layer_fill(dissem_ctx *ctx, int node, int layer, int kind, uint64_t s
             break;
         default: return set_error(DISSEM_EINVAL, "unknown fill kind %d", kind);
     }
+    if (!lb->host) CUDA_TRY(mark_ready(*lb, *ds));
     return DISSEM_OK;
 }
 
@@ -999,6 +1100,7 @@ int dissem_layer_reset(dissem_ctx *ctx, int node, int layer) {
     if (lb->host) return DISSEM_OK;
     CUDA_TRY(cudaSetDevice(ds->dev));
     CUDA_TRY(cudaMemsetAsync(lb->base + lb->trailer_off(), 0, (size_t)lb->trailer_bytes(), ds->stream));
+    CUDA_TRY(mark_ready(*lb, *ds));
     return DISSEM_OK;
 }
 
@@ -1016,28 +1118,70 @@ int dissem_layer_write(dissem_ctx *ctx, int node, int layer, const void *host, i
     if (!host) return set_error(DISSEM_EINVAL, "null host pointer");
     CUDA_TRY(cudaSetDevice(ds->dev));
     CUDA_TRY(cudaMemcpyAsync(lb->base + off, host, (size_t)size, cudaMemcpyHostToDevice, ds->stream));
+    if (!lb->host) CUDA_TRY(mark_ready(*lb, *ds));
     return DISSEM_OK;
+}
+
+// ---- read-back side ---------------------------------------------------------------------------------------------
+// Reads of a layer (bytes, checksum table, received counter, verify pass) follow one discipline: look the buffer up under
+// ctx->mu and copy what is needed out of the store; RELEASE ctx->mu; wait for the streams that may still be writing the
+// buffer (its owner's and those recorded in LayerBuf::writers); then copy on the owner's read stream.  Other threads
+// keep calling dissem_send meanwhile (the reference issues one goroutine per Send, node.go:343, :598).  The caller must
+// not free a layer another thread is reading.
+struct LayerView {
+    uint8_t *base = nullptr;
+    int64_t size = 0, n_chunks = 0, trailer_off = 0;
+    bool host = false;
+    int dev_slot = -1;
+    std::vector<int> wait_slots;       // device slots whose transfer stream may still be writing the buffer
+};
+
+// caller holds ctx->mu
+static int view_layer(dissem_ctx *ctx, int node, int layer, LayerView *v) {
+    LayerBuf *lb = nullptr;
+    int rc = find_layer(ctx, node, layer, &lb);
+    if (rc) return rc;
+    DeviceState *ds = nullptr;
+    rc = local_dev(ctx, node, &ds);
+    if (rc) return rc;
+    v->base = lb->base;
+    v->size = lb->size;
+    v->n_chunks = lb->n_chunks();
+    v->trailer_off = lb->trailer_off();
+    v->host = lb->host;
+    v->dev_slot = ctx->node_dev_slot[node];
+    v->wait_slots.push_back(v->dev_slot);
+    for (int sl = 0; sl < (int)ctx->devs.size() && sl < 64; ++sl)
+        if (sl != v->dev_slot && ((lb->writers >> sl) & 1ull)) v->wait_slots.push_back(sl);
+    return 0;
+}
+
+// no lock held (ctx->devs is fixed after dissem_init)
+static int wait_writers(dissem_ctx *ctx, const LayerView &v) {
+    for (int sl : v.wait_slots) {
+        CUDA_TRY(cudaSetDevice(ctx->devs[sl].dev));
+        CUDA_TRY(cudaStreamSynchronize(ctx->devs[sl].stream));
+    }
+    return 0;
 }
 
 int dissem_layer_read(dissem_ctx *ctx, int node, int layer, void *host, int64_t off, int64_t size) {
     if (!ctx) return set_error(DISSEM_EINVAL, "null context");
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    LayerBuf *lb = nullptr;
-    DeviceState *ds = nullptr;
-    int rc = find_layer(ctx, node, layer, &lb);
-    if (rc) return rc;
-    rc = local_dev(ctx, node, &ds);
-    if (rc) return rc;
-    if (off < 0 || size < 0 || off + size > lb->size) return set_error(DISSEM_ERANGE, "read [%lld,+%lld) outside layer of %lld bytes", (long long)off, (long long)size, (long long)lb->size);
+    LayerView v;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        int rc = view_layer(ctx, node, layer, &v);
+        if (rc) return rc;
+    }
+    if (off < 0 || size < 0 || off + size > v.size) return set_error(DISSEM_ERANGE, "read [%lld,+%lld) outside layer of %lld bytes", (long long)off, (long long)size, (long long)v.size);
     if (size == 0) return DISSEM_OK;
     if (!host) return set_error(DISSEM_EINVAL, "null host pointer");
-    for (auto &d : ctx->devs) {           // a peer GPU may still be pushing into this layer
-        CUDA_TRY(cudaSetDevice(d.dev));
-        CUDA_TRY(cudaStreamSynchronize(d.stream));
-    }
-    CUDA_TRY(cudaSetDevice(ds->dev));
-    CUDA_TRY(cudaMemcpyAsync(host, lb->base + off, (size_t)size, cudaMemcpyDeviceToHost, ds->stream));
-    CUDA_TRY(cudaStreamSynchronize(ds->stream));
+    int rc = wait_writers(ctx, v);
+    if (rc) return rc;
+    DeviceState &ds = ctx->devs[v.dev_slot];
+    CUDA_TRY(cudaSetDevice(ds.dev));
+    CUDA_TRY(cudaMemcpyAsync(host, v.base + off, (size_t)size, cudaMemcpyDeviceToHost, ds.rd_stream));
+    CUDA_TRY(cudaStreamSynchronize(ds.rd_stream));
     return DISSEM_OK;
 }
 
@@ -1143,6 +1287,9 @@ int dissem_layer_export(dissem_ctx *ctx, int node, int layer, uint8_t handle_out
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     cudaIpcMemHandle_t h;
     CUDA_TRY(cudaSetDevice(lb->device));
+    // the peer process cannot wait for this process's stream: whatever the owner enqueued for the buffer (trailer
+    // zeroing, fill, upload) has completed before the handle leaves
+    if (ctx->node_dev_slot[node] >= 0) CUDA_TRY(cudaStreamSynchronize(ctx->devs[ctx->node_dev_slot[node]].stream));
     CUDA_TRY(cudaIpcGetMemHandle(&h, lb->base));
     memcpy(handle_out, &h, 64);
     return DISSEM_OK;
@@ -1179,6 +1326,10 @@ int dissem_layer_export_fd(dissem_ctx *ctx, int node, int layer, int *fd_out) {
     int rc = find_layer(ctx, node, layer, &lb);
     if (rc) return rc;
     if (!lb->vmm || lb->imported) return set_error(DISSEM_EINVAL, "layer %d of node %d is not a locally owned shareable VMM layer (set alloc_vmm = 2 before allocating)", layer, node);
+    if (ctx->node_dev_slot[node] >= 0) {             // as in dissem_layer_export: nothing of the owner's is still in flight
+        CUDA_TRY(cudaSetDevice(ctx->devs[ctx->node_dev_slot[node]].dev));
+        CUDA_TRY(cudaStreamSynchronize(ctx->devs[ctx->node_dev_slot[node]].stream));
+    }
     std::string err = vmm_export_fd(lb->blk, fd_out);
     if (!err.empty()) return set_error(DISSEM_ECUDA, "%s", err.c_str());
     return DISSEM_OK;
@@ -1564,91 +1715,193 @@ int dissem_poll(dissem_ctx *ctx, dissem_ticket ticket, int *done_out) {
         else if (e != cudaSuccess) return set_error(DISSEM_ECUDA, "transfer failed: %s", cudaGetErrorString(e));
     }
     *done_out = done;
+    if (done) {
+        // the kernels are done with the descriptor table: give the parked schedule (dissem_schedule_submit / dissem_send)
+        // back now, so that a caller who only ever polls does not exhaust the descriptor pool.  The ticket itself (its
+        // events, its timings) stays until dissem_wait or dissem_ticket_release.
+        auto sit = ctx->scheds.find(-ticket);
+        if (sit != ctx->scheds.end()) {
+            free_sched(ctx, sit->second);
+            ctx->scheds.erase(sit);
+        }
+    }
     return DISSEM_OK;
 }
 
-static int read_trailer(dissem_ctx *ctx, int node, int layer, int64_t byte_off, void *out, int64_t bytes) {
-    LayerBuf *lb = nullptr;
-    DeviceState *ds = nullptr;
-    int rc = find_layer(ctx, node, layer, &lb);
-    if (rc) return rc;
-    if (lb->host) return set_error(DISSEM_ENOTSUP, "an attached host layer has no checksum table or received counter (it is a source)");
-    rc = local_dev(ctx, node, &ds);
-    if (rc) return rc;
-    for (auto &d : ctx->devs) {
-        CUDA_TRY(cudaSetDevice(d.dev));
-        CUDA_TRY(cudaStreamSynchronize(d.stream));
+int dissem_ticket_release(dissem_ctx *ctx, dissem_ticket ticket) {
+    if (!ctx) return set_error(DISSEM_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->tickets.find(ticket);
+    if (it == ctx->tickets.end()) return set_error(DISSEM_ENOENT, "unknown ticket %lld", (long long)ticket);
+    for (auto &p : it->second.parts) {
+        cudaError_t e = cudaEventQuery(p.end);
+        if (e == cudaErrorNotReady) {
+            cudaGetLastError();
+            return set_error(DISSEM_EINVAL, "ticket %lld is still in flight: poll until done, or wait", (long long)ticket);
+        }
     }
-    CUDA_TRY(cudaSetDevice(ds->dev));
-    CUDA_TRY(cudaMemcpyAsync(out, lb->base + lb->trailer_off() + byte_off, (size_t)bytes, cudaMemcpyDeviceToHost, ds->stream));
-    CUDA_TRY(cudaStreamSynchronize(ds->stream));
+    drop_ticket(ctx, it->second);
+    ctx->tickets.erase(it);
+    auto sit = ctx->scheds.find(-ticket);
+    if (sit != ctx->scheds.end()) {
+        free_sched(ctx, sit->second);
+        ctx->scheds.erase(sit);
+    }
+    return DISSEM_OK;
+}
+
+static int read_trailer(dissem_ctx *ctx, int node, int layer, int64_t byte_off, void *out, int64_t bytes, int64_t expect_chunks) {
+    LayerView v;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        int rc = view_layer(ctx, node, layer, &v);
+        if (rc) return rc;
+    }
+    if (v.host) return set_error(DISSEM_ENOTSUP, "an attached host layer has no checksum table or received counter (it is a source)");
+    if (expect_chunks >= 0 && expect_chunks != v.n_chunks)
+        return set_error(DISSEM_EINVAL, "layer %d has %lld chunks, caller passed %lld", layer, (long long)v.n_chunks, (long long)expect_chunks);
+    if (bytes == 0) return DISSEM_OK;
+    int rc = wait_writers(ctx, v);
+    if (rc) return rc;
+    DeviceState &ds = ctx->devs[v.dev_slot];
+    CUDA_TRY(cudaSetDevice(ds.dev));
+    CUDA_TRY(cudaMemcpyAsync(out, v.base + v.trailer_off + byte_off, (size_t)bytes, cudaMemcpyDeviceToHost, ds.rd_stream));
+    CUDA_TRY(cudaStreamSynchronize(ds.rd_stream));
     return DISSEM_OK;
 }
 
 int dissem_layer_checksums(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks) {
-    if (!ctx || (!out && n_chunks > 0)) return set_error(DISSEM_EINVAL, "dissem_layer_checksums: bad arguments");
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    LayerBuf *lb = nullptr;
-    int rc = find_layer(ctx, node, layer, &lb);
-    if (rc) return rc;
-    if (n_chunks != lb->n_chunks()) return set_error(DISSEM_EINVAL, "layer %d has %lld chunks, caller passed %lld", layer, (long long)lb->n_chunks(), (long long)n_chunks);
-    if (n_chunks == 0) return DISSEM_OK;
-    return read_trailer(ctx, node, layer, 256, out, n_chunks * 16);
+    if (!ctx || (!out && n_chunks > 0) || n_chunks < 0) return set_error(DISSEM_EINVAL, "dissem_layer_checksums: bad arguments");
+    return read_trailer(ctx, node, layer, 256, out, n_chunks * 16, n_chunks);
 }
 
 int dissem_layer_received(dissem_ctx *ctx, int node, int layer, int64_t *bytes_out) {
     if (!ctx || !bytes_out) return set_error(DISSEM_EINVAL, "dissem_layer_received: bad arguments");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     unsigned long long v = 0;
-    int rc = read_trailer(ctx, node, layer, 0, &v, 8);
+    int rc = read_trailer(ctx, node, layer, 0, &v, 8, -1);
     if (rc) return rc;
     *bytes_out = (int64_t)v;
     return DISSEM_OK;
 }
 
+// The fused tables of several local layers with one device-side gather and ONE device-to-host copy per GPU (what a
+// leader reads after a batch: one table per (node, layer) of its Assignment).  out receives the tables back to back in
+// the order given; total_chunks = sum of the layers' chunk counts.
+int dissem_layers_checksums(dissem_ctx *ctx, const int *nodes, const int *layers, int n, uint64_t *out, int64_t total_chunks) {
+    if (!ctx || n < 0 || (n > 0 && (!nodes || !layers)) || (total_chunks > 0 && !out) || total_chunks < 0)
+        return set_error(DISSEM_EINVAL, "dissem_layers_checksums: bad arguments");
+    std::vector<LayerView> views((size_t)n);
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        int64_t sum = 0;
+        for (int i = 0; i < n; ++i) {
+            int rc = view_layer(ctx, nodes[i], layers[i], &views[i]);
+            if (rc) return rc;
+            if (views[i].host) return set_error(DISSEM_ENOTSUP, "layer %d of node %d is attached host memory: no checksum table", layers[i], nodes[i]);
+            sum += views[i].n_chunks;
+        }
+        if (sum != total_chunks) return set_error(DISSEM_EINVAL, "the %d layers have %lld chunks in all, caller passed %lld", n, (long long)sum, (long long)total_chunks);
+    }
+    std::vector<char> waited(ctx->devs.size(), 0);
+    for (auto &v : views)
+        for (int sl : v.wait_slots)
+            if (!waited[sl]) {
+                waited[sl] = 1;
+                CUDA_TRY(cudaSetDevice(ctx->devs[sl].dev));
+                CUDA_TRY(cudaStreamSynchronize(ctx->devs[sl].stream));
+            }
+    // per owning GPU: gather list -> arena, gather kernel -> arena, one copy -> pinned arena -> out
+    for (size_t sl = 0; sl < ctx->devs.size(); ++sl) {
+        DeviceState &ds = ctx->devs[sl];
+        std::vector<GatherItem> items;
+        std::vector<std::pair<int64_t, int64_t>> place;          // (offset in out, bytes) per item
+        int64_t out_off = 0, arena_off = 0;
+        for (int i = 0; i < n; ++i) {
+            const int64_t bytes = views[i].n_chunks * 16;
+            if (views[i].dev_slot == (int)sl && bytes > 0) {
+                GatherItem g;
+                g.src = reinterpret_cast<const unsigned long long *>(views[i].base + views[i].trailer_off + 256);
+                g.dst_word = arena_off / 8;
+                g.words = bytes / 8;
+                items.push_back(g);
+                place.emplace_back(out_off, bytes);
+                arena_off += bytes;
+            }
+            out_off += bytes;
+        }
+        if (items.empty()) continue;
+        std::lock_guard<std::mutex> arena_lock(*ds.arena_mu);
+        CUDA_TRY(cudaSetDevice(ds.dev));
+        const size_t list_bytes = align_up((int64_t)(items.size() * sizeof(GatherItem)), 256);
+        if (list_bytes + (size_t)arena_off > ds.arena_bytes) {
+            // beyond the arena (more than ~2 MiB of tables on one GPU): fall back to one copy per layer, still lock-free
+            for (size_t k = 0; k < items.size(); ++k)
+                CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<uint8_t *>(out) + place[k].first, items[k].src, (size_t)place[k].second,
+                                         cudaMemcpyDeviceToHost, ds.rd_stream));
+            CUDA_TRY(cudaStreamSynchronize(ds.rd_stream));
+            continue;
+        }
+        memcpy(ds.arena_host, items.data(), items.size() * sizeof(GatherItem));
+        CUDA_TRY(cudaMemcpyAsync(ds.arena_dev, ds.arena_host, items.size() * sizeof(GatherItem), cudaMemcpyHostToDevice, ds.rd_stream));
+        CUDA_TRY(launch_gather_tables(reinterpret_cast<const GatherItem *>(ds.arena_dev), (int)items.size(),
+                                      reinterpret_cast<unsigned long long *>(ds.arena_dev + list_bytes), ds.n_sm, ds.rd_stream));
+        CUDA_TRY(cudaMemcpyAsync(ds.arena_host + list_bytes, ds.arena_dev + list_bytes, (size_t)arena_off, cudaMemcpyDeviceToHost, ds.rd_stream));
+        CUDA_TRY(cudaStreamSynchronize(ds.rd_stream));
+        int64_t pos = 0;
+        for (size_t k = 0; k < items.size(); ++k) {
+            memcpy(reinterpret_cast<uint8_t *>(out) + place[k].first, ds.arena_host + list_bytes + pos, (size_t)place[k].second);
+            pos += place[k].second;
+        }
+    }
+    return DISSEM_OK;
+}
+
 int dissem_layer_verify(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks) {
     if (!ctx || (!out && n_chunks > 0)) return set_error(DISSEM_EINVAL, "dissem_layer_verify: bad arguments");
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    LayerBuf *lb = nullptr;
-    DeviceState *ds = nullptr;
-    int rc = find_layer(ctx, node, layer, &lb);
-    if (rc) return rc;
-    rc = local_dev(ctx, node, &ds);
-    if (rc) return rc;
-    if (n_chunks != lb->n_chunks()) return set_error(DISSEM_EINVAL, "layer %d has %lld chunks, caller passed %lld", layer, (long long)lb->n_chunks(), (long long)n_chunks);
-    if (n_chunks == 0) return DISSEM_OK;
-    for (auto &d : ctx->devs) {
-        CUDA_TRY(cudaSetDevice(d.dev));
-        CUDA_TRY(cudaStreamSynchronize(d.stream));
+    LayerView v;
+    LaunchCfg cfg{};
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        int rc = view_layer(ctx, node, layer, &v);
+        if (rc) return rc;
+        cfg = LaunchCfg{ctx->devs[v.dev_slot].n_sm, (int)ctx->opt_ctas_per_sm, v.host ? 0 : (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
     }
-    CUDA_TRY(cudaSetDevice(ds->dev));
-    // scratch: a descriptor and a fresh checksum table
-    uint8_t *scratch = nullptr;
+    if (n_chunks != v.n_chunks) return set_error(DISSEM_EINVAL, "layer %d has %lld chunks, caller passed %lld", layer, (long long)v.n_chunks, (long long)n_chunks);
+    if (n_chunks == 0) return DISSEM_OK;
+    int rc = wait_writers(ctx, v);
+    if (rc) return rc;
+    DeviceState &ds = ctx->devs[v.dev_slot];
+    // scratch (counters, one descriptor, a fresh table) comes from the GPU's arena: nothing is allocated or freed here
     const size_t table_bytes = (size_t)n_chunks * 16;
-    CUDA_TRY(cudaMalloc(&scratch, 256 + table_bytes));
+    if (512 + table_bytes > ds.arena_bytes)
+        return set_error(DISSEM_ERANGE, "layer %d has %lld chunks; the verify arena holds %lld", layer, (long long)n_chunks,
+                         (long long)((ds.arena_bytes - 512) / 16));
+    std::lock_guard<std::mutex> arena_lock(*ds.arena_mu);
+    CUDA_TRY(cudaSetDevice(ds.dev));
+    uint8_t *scratch = ds.arena_dev;
     XferDesc d;
     memset(&d, 0, sizeof d);
-    d.src = lb->base;
+    d.src = v.base;
     d.dst = nullptr;
-    d.csum = reinterpret_cast<unsigned long long *>(scratch + 256);
+    d.csum = reinterpret_cast<unsigned long long *>(scratch + 512);
     d.received = nullptr;
     d.off = 0;
-    d.size = lb->size;
-    d.total = lb->size;
+    d.size = v.size;
+    d.total = v.size;
     d.first_unit = 0;
-    int result = DISSEM_OK;
-    cudaError_t e = cudaMemsetAsync(scratch, 0, 256 + table_bytes, ds->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(scratch, &d, sizeof d, cudaMemcpyHostToDevice, ds->stream);
-    if (e == cudaSuccess) {
-        LaunchCfg cfg{ds->n_sm, (int)ctx->opt_ctas_per_sm, lb->host ? 0 : (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
-        e = launch_copy_csum(reinterpret_cast<XferDesc *>(scratch), 1, units_of(0, lb->size, kChunkShift), kChunkShift,
-                             ds->counters, cfg, ds->stream, nullptr);
-    }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out, scratch + 256, table_bytes, cudaMemcpyDeviceToHost, ds->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ds->stream);
-    if (e != cudaSuccess) result = set_error(DISSEM_ECUDA, "verify pass failed: %s", cudaGetErrorString(e));
-    cudaFree(scratch);
-    return result;
+    // its own counters (first 16 bytes of the arena) and the read stream: the pass neither waits for nor delays transfers
+    memset(ds.arena_host, 0, 512);
+    memcpy(ds.arena_host + 256, &d, sizeof d);
+    cudaError_t e = cudaMemsetAsync(scratch + 512, 0, table_bytes, ds.rd_stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(scratch, ds.arena_host, 512, cudaMemcpyHostToDevice, ds.rd_stream);
+    if (e == cudaSuccess)
+        e = launch_copy_csum(reinterpret_cast<XferDesc *>(scratch + 256), 1, units_of(0, v.size, kChunkShift), kChunkShift,
+                             reinterpret_cast<SchedCounters *>(scratch), cfg, ds.rd_stream, nullptr);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ds.arena_host + 512, scratch + 512, table_bytes, cudaMemcpyDeviceToHost, ds.rd_stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ds.rd_stream);
+    if (e != cudaSuccess) return set_error(DISSEM_ECUDA, "verify pass failed: %s", cudaGetErrorString(e));
+    memcpy(out, ds.arena_host + 512, table_bytes);
+    return DISSEM_OK;
 }
 
 int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {

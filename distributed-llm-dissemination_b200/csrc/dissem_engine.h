@@ -19,6 +19,14 @@ struct LayerBuf {
     bool host = false;      // a caller-owned pinned host buffer attached as this node's copy (source only, no trailer)
     bool vmm = false;       // allocated through the VMM API (can be bound to an NVLS multicast object)
     VmmBlock blk;
+    // cudaEvent_t (kept opaque here): recorded on the OWNER's stream after everything the owner enqueued that writes
+    // this buffer (trailer zeroing at alloc / reset, fill, host write).  A kernel of ANOTHER GPU's stream that reads or
+    // writes the buffer waits for it first; streams of different GPUs are not ordered otherwise.  NULL for imported
+    // and attached-host layers (their owner synchronises before handing out the handle / the memory).
+    void *ready = nullptr;
+    // bit s set: a kernel on local device slot s has been launched that writes this buffer (push from that GPU, pull or
+    // disk load by the owner).  A host read of the buffer waits for those streams (and the owner's), not for every GPU.
+    unsigned long long writers = 0;
 
     int64_t n_chunks() const;
     int64_t trailer_off() const;

@@ -273,6 +273,26 @@ __global__ void zero_csum_kernel(const XferDesc *__restrict__ descs, int n_descs
 }
 
 // ------------------------------------------------------------------------------------------------
+// checksum tables of several layers -> one contiguous buffer (one CTA per table, grid-stride)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_tables_kernel(const GatherItem *__restrict__ items, int n_items, unsigned long long *__restrict__ dst) {
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const unsigned long long *src = items[it].src;
+        unsigned long long *out = dst + items[it].dst_word;
+        const long long words = items[it].words;
+        for (long long w = threadIdx.x; w < words; w += blockDim.x) out[w] = src[w];
+    }
+}
+
+cudaError_t launch_gather_tables(const GatherItem *items, int n_items, unsigned long long *dst, int n_sm, cudaStream_t stream) {
+    if (n_items <= 0) return cudaSuccess;
+    const int grid = n_items < 4 * n_sm ? n_items : 4 * n_sm;
+    gather_tables_kernel<<<grid, 256, 0, stream>>>(items, n_items, dst);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
 // K6: synthetic layer contents
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
@@ -363,6 +383,7 @@ cudaError_t warm_kernels() {
     cudaError_t e = cudaFuncGetAttributes(&a, copy_csum_kernel<512, 4>);
     if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, zero_csum_kernel);
     if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, fill_pattern_kernel);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, gather_tables_kernel);
     if (e == cudaSuccess) e = warm_kernels_tma();
     return e;
 }

@@ -66,6 +66,16 @@ cudaError_t launch_copy_csum(const XferDesc *descs, int n_descs, long long total
                              SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream,
                              int *grid_out);
 
+// Gather of several checksum tables into one contiguous device buffer (dissem_layers_checksums: one device-to-host copy
+// per GPU instead of one per layer).  dst_word / words are in u64 units.
+struct GatherItem {
+    const unsigned long long *src;
+    long long dst_word;
+    long long words;
+    long long pad;
+};
+cudaError_t launch_gather_tables(const GatherItem *items, int n_items, unsigned long long *dst, int n_sm, cudaStream_t stream);
+
 // Force the module with these kernels to load on the current device (CUDA loads lazily: without this the first
 // transfer of a run would pay the load inside its timed region).
 cudaError_t warm_kernels();

@@ -44,16 +44,15 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocScratch
 
 constexpr int kMaxDevices = 64;
 struct PerDevice {
+    std::mutex mu;                      // one call at a time per GPU (each GPU has its own copy of the array)
     bool ready = false;
     unsigned char *scratch = nullptr;   // device address of g_noalloc_scratch on this GPU
     int n_sm = 0;
 };
-std::mutex g_mu;
 PerDevice g_dev[kMaxDevices];
 
-// Once per GPU, with that GPU current: resolve the array's device address and read the SM count.
+// Once per GPU, with that GPU current and its PerDevice::mu held: resolve the array's device address and read the SM count.
 int device_scratch(int device, PerDevice **out) {
-    if (device < 0 || device >= kMaxDevices) return dissem::set_error(DISSEM_EINVAL, "device %d out of range", device);
     PerDevice &pd = g_dev[device];
     if (!pd.ready) {
         void *ptr = nullptr;
@@ -99,7 +98,10 @@ extern "C" int dissem_checksum_noalloc(int device, const void *data, int64_t siz
         return set_error(DISSEM_EINVAL, "dissem_checksum_noalloc: data must be 16-byte aligned");
     if (size == 0) return DISSEM_OK;
 
-    std::lock_guard<std::mutex> lk(g_mu);      // host-side serialisation; GPU-side overlap is the caller's to avoid
+    if (device < 0 || device >= kMaxDevices) return set_error(DISSEM_EINVAL, "device %d out of range", device);
+    // Host-side serialisation per GPU: calls on different GPUs use different arrays and run side by side; calls on one
+    // GPU queue here.  GPU-side overlap through other streams of the caller's remains the caller's to avoid.
+    std::lock_guard<std::mutex> lk(g_dev[device].mu);
     int prev = -1;
     cudaError_t e = cudaGetDevice(&prev);
     if (e != cudaSuccess) {

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <tuple>
 #include <vector>
 
 #include "../../include/dissem.h"
@@ -36,6 +37,35 @@ int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, in
         const int64_t reverse = std::max(ingress[gs], egress[gd]);
         if (2 * reverse < forward) x.flags |= DISSEM_XFER_PULL;
     }
+    return DISSEM_OK;
+}
+
+int dissem_plan_align(dissem_xfer *xfers, int n, int *n_out) {
+    if (n < 0 || (n > 0 && !xfers) || !n_out) return set_error(DISSEM_EINVAL, "dissem_plan_align: bad arguments");
+    // fragments of one (destination, layer, round), ascending by offset
+    std::map<std::tuple<int, int, int>, std::vector<int>> groups;
+    for (int i = 0; i < n; ++i)
+        if (xfers[i].size > 0)
+            groups[std::make_tuple(xfers[i].dst_node, xfers[i].layer, (xfers[i].flags >> DISSEM_XFER_ROUND_SHIFT) & 0xFFFF)].push_back(i);
+    for (auto &kv : groups) {
+        std::vector<int> &g = kv.second;
+        if (g.size() < 2) continue;
+        std::sort(g.begin(), g.end(), [&](int a, int b) { return xfers[a].off < xfers[b].off; });
+        for (size_t k = 0; k + 1 < g.size(); ++k) {
+            dissem_xfer &a = xfers[g[k]], &b = xfers[g[k + 1]];
+            if (a.off + a.size != b.off || a.total != b.total) continue;          // not a cut of one contiguous range: leave it
+            const int64_t cut = b.off / DISSEM_CHUNK_BYTES * DISSEM_CHUNK_BYTES;  // the boundary moves DOWN to a chunk start
+            if (cut == b.off) continue;
+            const int64_t new_cut = std::max(cut, a.off);                         // a fragment shorter than the move vanishes
+            b.size += b.off - new_cut;
+            b.off = new_cut;
+            a.size = new_cut - a.off;
+        }
+    }
+    int m = 0;
+    for (int i = 0; i < n; ++i)
+        if (xfers[i].size > 0 || xfers[i].total == 0) xfers[m++] = xfers[i];
+    *n_out = m;
     return DISSEM_OK;
 }
 
@@ -125,6 +155,14 @@ int dissem_plan_optimize(const dissem_xfer *in, int n, const int *gpu_of_node, i
                 }
             }
         }
+    }
+    {
+        // fragment cuts (a flow plan) move to checksum-chunk boundaries: no table entry is then shared by two senders
+        int m = n;
+        int rc = dissem_plan_align(staged.data(), n, &m);
+        if (rc) return rc;
+        staged.resize((size_t)m);
+        n = m;
     }
     in = staged.data();
     // busiest-port bytes of a transfer list (transfers inside one GPU do not use a port)

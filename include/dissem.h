@@ -41,7 +41,7 @@ extern "C" {
 #define DISSEM_ENOENT -4   /* unknown node / layer / ticket / schedule */
 #define DISSEM_EEXIST -5   /* layer already present */
 #define DISSEM_ENOMEM -6
-#define DISSEM_ERANGE -7   /* offset/size outside the layer */
+#define DISSEM_ERANGE -7   /* offset/size outside the layer; a size beyond a fixed scratch limit (no-allocation entry point) */
 #define DISSEM_ENOTSUP -8  /* capability missing on this box (e.g. NVLS multicast) */
 #define DISSEM_EPARSE -9   /* malformed config JSON */
 #define DISSEM_EPLAN -10   /* the mode cannot serve this placement (e.g. mode 0, leader lacks a layer) */
@@ -111,8 +111,10 @@ int dissem_layer_fill(dissem_ctx *ctx, int node, int layer, int kind, uint64_t s
 /* Zero the checksum table and the received counter (a destination does this before a new run). */
 int dissem_layer_reset(dissem_ctx *ctx, int node, int layer);
 /* Host <-> HBM.  `host` may be any host memory; pinned memory from dissem_host_alloc makes the copy
- * asynchronous and full-speed.  write is ordered before later transfers on the node's stream; read
- * waits for everything submitted so far on the node's device. */
+ * asynchronous and full-speed.  write is ordered before every later transfer that reads or writes the layer, whichever
+ * GPU executes it (the same holds for alloc, fill and reset: each buffer carries an event the executing stream waits
+ * for).  read waits for the transfers submitted so far that write THIS layer (not for the rest of the device), without
+ * holding the context's lock: other threads keep sending meanwhile.  Do not free a layer that another thread reads. */
 int dissem_layer_write(dissem_ctx *ctx, int node, int layer, const void *host, int64_t off, int64_t size);
 int dissem_layer_read(dissem_ctx *ctx, int node, int layer, void *host, int64_t off, int64_t size);
 int dissem_host_alloc(void **out, int64_t size); /* pinned, GPU-mapped host memory for layer bytes */
@@ -193,6 +195,17 @@ int dissem_schedule_info(dissem_ctx *ctx, dissem_sched sched, int64_t *units_out
  * every process of a job computes the same answer from the same plan. */
 int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, int n_nodes);
 
+/* Fragment cuts on checksum-chunk boundaries (no counterpart in the reference, whose fragments are never checked).
+ * flow.go cuts a layer wherever the max-flow solution falls (flow.go:193-212), so two senders usually share one
+ * 256 KiB checksum chunk at every cut; their partial sums then meet in one table entry, which costs a zeroing owner,
+ * cross-GPU ordering on every relaunch, and cannot be re-zeroed at all when the two senders are different processes.
+ * Where consecutive fragments of one (destination, layer) are a cut of one contiguous range, this moves each internal
+ * boundary DOWN to a multiple of DISSEM_CHUNK_BYTES (the later fragment's sender, which holds the whole layer as every
+ * LayerSrc does, sends up to 256 KiB more; a fragment that shrinks to nothing is dropped).  In place; *n_out = the
+ * number of transfers left.  Coverage and destinations are unchanged, so the delivered store is identical.
+ * dissem_plan_optimize applies it first.  Pure host logic. */
+int dissem_plan_align(dissem_xfer *xfers, int n, int *n_out);
+
 /* Relay / pipelined forwarding (generalises the reference's tee-pipe, transport.go:145-196, and mode 1's peer
  * retransmission, node.go:1462-1484, to piece granularity).  Rewrites a plan: transfers of the same bytes from one
  * source to k destinations become a chain  source -> d0 -> d1 -> ...  cut into `pieces` pieces (boundaries at multiples
@@ -221,16 +234,27 @@ int dissem_wait(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out);
 /* As dissem_wait; copy_ms_out (may be NULL) is the device time of the copy+checksum kernel alone (the batch
  * also runs a tiny kernel that zeroes the checksum entries it is about to fill). */
 int dissem_wait_detail(dissem_ctx *ctx, dissem_ticket ticket, double *ms_out, double *copy_ms_out);
+/* Non-blocking.  Every ticket must eventually be handed to dissem_wait (which consumes it) or, once dissem_poll has
+ * reported it done, to dissem_ticket_release; otherwise its events stay allocated until dissem_close. */
 int dissem_poll(dissem_ctx *ctx, dissem_ticket ticket, int *done_out);
+int dissem_ticket_release(dissem_ctx *ctx, dissem_ticket ticket);   /* DISSEM_EINVAL while the batch is in flight */
 
 /* ---- delivery verification (no counterpart in the reference, which never checks content) ----------- */
 /* Per-chunk checksums accumulated by the copy pass at the DESTINATION copy of the layer:
  * out[2c] = A_c, out[2c+1] = B_c, n_chunks = ceil(size / DISSEM_CHUNK_BYTES).  Definition in DESIGN.md §4. */
 int dissem_layer_checksums(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks);
-/* Independent read-only pass over the layer as it now sits in HBM; same format. */
+/* The same for n local (node, layer) pairs at once: the tables back to back in `out`, in the order given, total_chunks =
+ * the sum of their chunk counts.  One gather kernel and one device-to-host copy per GPU, instead of a synchronising copy
+ * per layer (what a leader reads after a batch: one table per pair of its Assignment). */
+int dissem_layers_checksums(dissem_ctx *ctx, const int *nodes, const int *layers, int n, uint64_t *out,
+                            int64_t total_chunks);
+/* Independent read-only pass over the layer as it now sits in HBM; same format.  Its scratch comes from an arena set
+ * up by dissem_init (no allocation per call); layers beyond 128 Ki chunks (32 GiB) fail with DISSEM_ERANGE. */
 int dissem_layer_verify(dissem_ctx *ctx, int node, int layer, uint64_t *out, int64_t n_chunks);
 /* Bytes received so far for the layer (the counter FlowRetransmitReceiverNode keeps in
- * layerSrc.DataSize, node.go:1542; the ack condition is received == total, node.go:1555). */
+ * layerSrc.DataSize, node.go:1542; the ack condition is received == total, node.go:1555).  Monotonic: it is zeroed by
+ * dissem_layer_alloc / dissem_layer_reset only, so launching a schedule twice counts twice.  An NVLS multicast stream
+ * also adds to the SOURCE's own counter and checksum table (the source's copy is a member of the multicast object). */
 int dissem_layer_received(dissem_ctx *ctx, int node, int layer, int64_t *bytes_out);
 
 /* ---- for callers that cannot allocate device memory (no counterpart in the reference) ----------------- */
@@ -246,6 +270,8 @@ int dissem_layer_received(dissem_ctx *ctx, int node, int layer, int64_t *bytes_o
  *   - all calls on a GPU share the one array; each call clears the part it uses first, so results do not depend
  *     on earlier calls, but two calls whose GPU work may overlap (other streams or threads) corrupt each other:
  *     run them one after another;
+ *   - calls on one GPU are serialised on the host (a per-GPU lock held until the stream has finished); calls on
+ *     different GPUs run side by side, each GPU has its own copy of the array;
  *   - the first call on each GPU resolves the array's device address; make that first call at start-up, before
  *     any stream capture begins on that GPU.
  * device: CUDA ordinal that owns `data`.  data: device pointer, size bytes.  out: HOST array of 2*n_chunks

@@ -283,6 +283,36 @@ def test_plan_optimize_picks_relay_only_when_it_unloads_the_busiest_port():
     assert pieces == 0 and all(x.flags == 0 for x in one)
 
 
+def test_plan_align_moves_cuts_to_chunk_boundaries_and_keeps_coverage():
+    """dissem_plan_align on flow plans (mode 3 cuts a layer wherever the max flow falls, flow.go:193-212): afterwards no two
+    fragments share a 256 KiB checksum chunk, and every (destination, layer) is still covered exactly once."""
+    C = d.CHUNK_BYTES
+    for text, scale in ((o.config_stage_ring(8, 32, o.S2), 1_000_000), (o.config_stage_ring(8, 32, o.S2, ring=False), 1_000_000),
+                        (o.config_conf_json(), 1), (o.config_stage_ring(4, 8, (1 << 20) + 52), 1_000_000)):
+        xs = d.parse_plan(d.plan(text, 3, time_scale=scale))
+        al = d.plan_align(xs)
+        cover_before, cover_after = {}, {}
+        for lst, cov in ((xs, cover_before), (al, cover_after)):
+            for x in lst:
+                cov.setdefault((x.dst_node, x.layer, x.total), []).append((x.off, x.off + x.size))
+        assert set(cover_before) == set(cover_after)
+        for key, spans in cover_after.items():
+            spans.sort()
+            assert spans[0][0] == min(a for a, _b in cover_before[key]) and spans[-1][1] == max(b for _a, b in cover_before[key])
+            for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+                assert a1 == b0 and b0 % C == 0                              # contiguous, cut on a chunk boundary
+        assert all(x.size > 0 for x in al)
+        # every fragment still comes from a node that holds the layer (any sender holds the WHOLE layer)
+        holders = {(x.src_node, x.layer) for x in xs}
+        assert all((x.src_node, x.layer) in holders for x in al)
+    # a fragment smaller than the move disappears; unrelated and non-contiguous transfers are left alone
+    tiny = [d.Xfer(0, 3, 7, 0, 0, C + 100, 4 * C), d.Xfer(1, 3, 7, 0, C + 100, 50, 4 * C), d.Xfer(2, 3, 7, 0, C + 150, 3 * C - 150, 4 * C),
+            d.Xfer(0, 4, 7, 0, 10, 20, 4 * C), d.Xfer(1, 4, 7, 0, 100, 20, 4 * C)]
+    al = d.plan_align(tiny)
+    rows = sorted((x.src_node, x.dst_node, x.off, x.size) for x in al)
+    assert rows == sorted([(0, 3, 0, C), (2, 3, C, 3 * C), (0, 4, 10, 20), (1, 4, 100, 20)])
+
+
 def test_plan_digests_are_stable():
     """Every BASELINE configuration x mode: the C++ planners still produce the committed plans (tests/golden/plan_digests.json),
     and the oracle agrees with each of them where it restates the mode."""
