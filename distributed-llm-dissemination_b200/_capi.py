@@ -85,6 +85,8 @@ def load_library() -> ctypes.CDLL:
         "dissem_schedule_info": (c.c_int, [P, i64, c.POINTER(i64), c.POINTER(c.c_int), c.POINTER(i64)]),
         "dissem_plan_directions": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int]),
         "dissem_plan_align": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int)]),
+        "dissem_plan_localize": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.c_int), c.POINTER(c.c_int),
+                                           c.c_int, c.POINTER(c.c_int)]),
         "dissem_plan_relay": (c.c_int, [c.POINTER(Xfer), c.c_int, c.c_int, c.POINTER(c.POINTER(Xfer)), c.POINTER(c.c_int)]),
         "dissem_plan_optimize": (c.c_int, [c.POINTER(Xfer), c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.POINTER(Xfer)),
                                            c.POINTER(c.c_int), c.POINTER(c.c_int)]),
@@ -151,6 +153,19 @@ def plan_align(xfers: List["Xfer"]) -> List["Xfer"]:
     arr = make_xfers(xfers)
     m = ctypes.c_int()
     _check(lib().dissem_plan_align(arr, len(xfers), ctypes.byref(m)))
+    return [Xfer(a.src_node, a.dst_node, a.layer, a.flags, a.off, a.size, a.total) for a in arr[:m.value]]
+
+
+def plan_localize(xfers: List["Xfer"], gpu_of_node: Sequence[int], holders: Sequence) -> List["Xfer"]:
+    """dissem_plan_localize: transfers that cross GPUs although a node on the destination's GPU holds the layer are
+    re-sourced from that node.  holders: (node, layer) pairs of HBM-resident whole layers."""
+    arr = make_xfers(xfers)
+    holders = list(holders)
+    g = (ctypes.c_int * len(gpu_of_node))(*gpu_of_node)
+    hn = (ctypes.c_int * max(len(holders), 1))(*[h[0] for h in holders])
+    hl = (ctypes.c_int * max(len(holders), 1))(*[h[1] for h in holders])
+    m = ctypes.c_int()
+    _check(lib().dissem_plan_localize(arr, len(xfers), g, len(gpu_of_node), hn, hl, len(holders), ctypes.byref(m)))
     return [Xfer(a.src_node, a.dst_node, a.layer, a.flags, a.off, a.size, a.total) for a in arr[:m.value]]
 
 

@@ -69,6 +69,52 @@ int dissem_plan_align(dissem_xfer *xfers, int n, int *n_out) {
     return DISSEM_OK;
 }
 
+int dissem_plan_localize(dissem_xfer *xfers, int n, const int *gpu_of_node, int n_nodes, const int *holder_nodes,
+                         const int *holder_layers, int n_holders, int *n_out) {
+    if (n < 0 || (n > 0 && !xfers) || !gpu_of_node || n_nodes <= 0 || n_holders < 0 || (n_holders > 0 && (!holder_nodes || !holder_layers)) || !n_out)
+        return set_error(DISSEM_EINVAL, "dissem_plan_localize: bad arguments");
+    std::map<std::pair<int, int>, int> local_holder;          // (gpu, layer) -> lowest node id on that GPU holding the layer
+    for (int i = 0; i < n_holders; ++i) {
+        if (holder_nodes[i] < 0 || holder_nodes[i] >= n_nodes) return set_error(DISSEM_ENOENT, "holder %d names a node outside [0,%d)", i, n_nodes);
+        auto key = std::make_pair(gpu_of_node[holder_nodes[i]], holder_layers[i]);
+        auto it = local_holder.find(key);
+        if (it == local_holder.end() || holder_nodes[i] < it->second) local_holder[key] = holder_nodes[i];
+    }
+    for (int i = 0; i < n; ++i) {
+        dissem_xfer &x = xfers[i];
+        if (x.src_node < 0 || x.src_node >= n_nodes || x.dst_node < 0 || x.dst_node >= n_nodes)
+            return set_error(DISSEM_ENOENT, "transfer %d names a node outside [0,%d)", i, n_nodes);
+        if ((x.flags & DISSEM_XFER_FILE) || gpu_of_node[x.src_node] == gpu_of_node[x.dst_node]) continue;
+        auto it = local_holder.find(std::make_pair(gpu_of_node[x.dst_node], x.layer));
+        if (it == local_holder.end() || it->second == x.dst_node) continue;
+        x.src_node = it->second;                               // same bytes, read from the copy that shares the GPU
+        x.flags &= ~DISSEM_XFER_PULL;
+    }
+    // fragments that now have the same source and touch each other become one transfer
+    std::vector<int> order((size_t)n);
+    for (int i = 0; i < n; ++i) order[(size_t)i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+        const dissem_xfer &x = xfers[a], &y = xfers[b];
+        return std::make_tuple(x.dst_node, x.layer, x.flags, x.src_node, x.off) < std::make_tuple(y.dst_node, y.layer, y.flags, y.src_node, y.off);
+    });
+    std::vector<dissem_xfer> merged;
+    for (int idx : order) {
+        const dissem_xfer &x = xfers[idx];
+        if (!merged.empty()) {
+            dissem_xfer &m = merged.back();
+            if (m.dst_node == x.dst_node && m.layer == x.layer && m.flags == x.flags && m.src_node == x.src_node && m.total == x.total &&
+                m.off + m.size == x.off && x.size > 0 && m.size > 0) {
+                m.size += x.size;
+                continue;
+            }
+        }
+        merged.push_back(x);
+    }
+    for (size_t i = 0; i < merged.size(); ++i) xfers[i] = merged[i];
+    *n_out = (int)merged.size();
+    return DISSEM_OK;
+}
+
 int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **out, int *n_out) {
     if (n < 0 || (n > 0 && !in) || !out || !n_out || pieces < 1 || pieces > 4096)
         return set_error(DISSEM_EINVAL, "dissem_plan_relay: bad arguments");

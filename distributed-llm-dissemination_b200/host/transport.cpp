@@ -165,6 +165,23 @@ int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *de
     for (auto &x : xfers)
         from_file.push_back(dissem_layer_info(fabric_->ctx(), (int)x.Src, (int)x.Layer, nullptr, nullptr) == DISSEM_ENOENT &&
                             dissem_layer_file_info(fabric_->ctx(), (int)x.Src, (int)x.Layer, nullptr) == DISSEM_OK);
+    // who holds which of the plan's layers in HBM right now (before destination buffers exist): lets the plan take a layer
+    // from a node that shares the destination's GPU instead of across NVLink (dissem_plan_localize)
+    const int n_nodes_all = dissem_n_nodes(fabric_->ctx());
+    std::vector<int> holder_nodes, holder_layers;
+    {
+        std::vector<int> layers_seen;
+        for (auto &x : xfers)
+            if (std::find(layers_seen.begin(), layers_seen.end(), (int)x.Layer) == layers_seen.end()) layers_seen.push_back((int)x.Layer);
+        for (int l : layers_seen)
+            for (int nd = 0; nd < n_nodes_all; ++nd) {
+                int64_t sz = 0;
+                if (dissem_layer_info(fabric_->ctx(), nd, l, &sz, nullptr) == DISSEM_OK) {
+                    holder_nodes.push_back(nd);
+                    holder_layers.push_back(l);
+                }
+            }
+    }
     for (auto &x : xfers) {
         int rc = EnsureDestLayer(x.Dest, x.Layer, x.TotalSize);
         if (rc) return rc;
@@ -192,6 +209,13 @@ int DeviceTransport::SendBatch(const std::vector<PlannedXfer> &xfers, double *de
     int rc = 0;
     dissem_ticket ticket = 0;
     // relay chains, push/pull directions, and for disk sources "read the file once, forward from HBM"
+    {
+        int m = (int)xs.size();
+        rc = dissem_plan_localize(xs.data(), m, gpu_of_node.data(), n_nodes, holder_nodes.data(), holder_layers.data(),
+                                  (int)holder_nodes.size(), &m);
+        if (rc) return rc;
+        xs.resize((size_t)m);
+    }
     rc = dissem_plan_optimize(xs.data(), (int)xs.size(), gpu_of_node.data(), n_nodes, &opt, &n_opt, nullptr);
     if (rc) return rc;
     rc = dissem_schedule_submit(fabric_->ctx(), opt, n_opt, &ticket);

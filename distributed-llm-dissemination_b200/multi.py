@@ -180,3 +180,131 @@ class FdExchange:
             self._os.unlink(self.path)
         except OSError:
             pass
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Placements and store set-up shared by bench.py and tools/ (one process per GPU)
+# ----------------------------------------------------------------------------------------------------------------
+def fanout_plan(xfer_cls, n_nodes: int, n_layers: int, size: int, one_seed: bool):
+    """BASELINE config 4: layer l -> {l, l+1, (l+2 if l%3>=1), (l+3 if l%3==2)} mod N, seeded on node
+    (l+4) mod N — or every layer on node 0 (`one_seed`).  Returns ({layer: seed node}, [transfers])."""
+    holders, xfers = {}, []
+    for l in range(n_layers):
+        seed = 0 if one_seed else (l + 4) % n_nodes
+        holders[l] = seed
+        dsts = [l % n_nodes, (l + 1) % n_nodes]
+        if l % 3 >= 1:
+            dsts.append((l + 2) % n_nodes)
+        if l % 3 == 2:
+            dsts.append((l + 3) % n_nodes)
+        for dst in sorted(set(dsts)):
+            if dst != seed:
+                xfers.append(xfer_cls(seed, dst, l, 0, 0, size, size))
+    return holders, xfers
+
+
+def remote_touches(xfers: Sequence, owner: Callable[[int], int], pull: bool = False) -> List[Tuple[int, int, int, int]]:
+    """(node, layer, total, executing rank) for every buffer that a kernel of ANOTHER rank than its owner touches."""
+    out = set()
+    for x in xfers:
+        ex, other = _sides(x, pull)
+        if owner(ex) != owner(other):
+            out.add((other, x.layer, x.total, owner(ex)))
+    return sorted(out)
+
+
+class SharedStore:
+    """Makes the buffers of this rank's nodes reachable from the ranks whose kernels touch them, and maps theirs here.
+    IPC handles (cudaMalloc'ed layers, all-gathered) by default; with `fx` (an FdExchange) the layers are shareable VMM
+    allocations and travel as file descriptors — the form NVLS multicast needs.  Every call is collective."""
+
+    def __init__(self, eng, dist, world: int, rank: int, owner: Callable[[int], int], fx=None):
+        self.eng, self.dist, self.world, self.rank, self.owner, self.fx = eng, dist, world, rank, owner, fx
+        self.imported = set()
+        self.sent = set()
+
+    def share(self, xfers: Sequence, pull: bool = False):
+        if self.dist is None:
+            return
+        touches = remote_touches(xfers, self.owner, pull)
+        if self.fx is None:
+            mine = {}
+            for (n, l, _t, _r) in touches:
+                if self.owner(n) == self.rank and (n, l) not in mine:
+                    mine[(n, l)] = self.eng.export(n, l)
+            handles = exchange_handles(self.dist, self.world, self.rank, mine)
+            for (n, l, total, r) in touches:
+                if r == self.rank and (n, l) not in self.imported:
+                    self.eng.import_(n, l, total, handles[(n, l)])
+                    self.imported.add((n, l))
+        else:
+            for (n, l, _t, r) in touches:
+                if self.owner(n) == self.rank and (n, l, r) not in self.sent:
+                    self.fx.send(r, f"buf:{n}:{l}:{r}", self.eng.export_fd(n, l))
+                    self.sent.add((n, l, r))
+            for (n, l, total, r) in touches:
+                if r == self.rank and (n, l) not in self.imported:
+                    self.eng.import_fd(n, l, total, self.fx.recv(f"buf:{n}:{l}:{r}"))
+                    self.imported.add((n, l))
+        self.dist.barrier()
+
+
+def mcast_groups(xfers: Sequence, owner: Callable[[int], int]) -> List[Tuple[int, int, List[int]]]:
+    """(layer, source node, [destination nodes]) for the transfers of the same whole bytes from one source to two or more
+    nodes, each on a GPU of its own — the groups the schedule compiler sends as one NVLS multicast stream."""
+    by: Dict[Tuple[int, int, int, int], List[int]] = {}
+    for x in xfers:
+        by.setdefault((x.layer, x.src_node, x.off, x.size), []).append(x.dst_node)
+    out = []
+    for (layer, src, _off, _size), dsts in sorted(by.items()):
+        ranks = [owner(src)] + [owner(d) for d in dsts]
+        if len(dsts) >= 2 and len(set(ranks)) == len(ranks):
+            out.append((layer, src, sorted(dsts)))
+    return out
+
+
+def setup_mcast(eng, fx, dist, groups: Sequence[Tuple[int, int, List[int]]], owner: Callable[[int], int], rank: int):
+    """Create (source's rank), join (destinations' ranks) and bind (everybody) one multicast object per group.  The
+    source's process must already have imported the destinations' copies (SharedStore with `fx`).  Collective: after
+    each phase the ranks agree on whether it worked, so a box without NVLS support makes every rank return
+    (False, reason) instead of leaving some of them waiting for descriptors that never come."""
+    import os
+
+    import torch
+
+    def agreed(ok: bool) -> bool:
+        f = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(f, op=dist.ReduceOp.MIN)
+        return bool(f.item())
+
+    why = ""
+    ok = True
+    try:
+        for (layer, src, dsts) in groups:
+            if owner(src) == rank:
+                fd = eng.mcast_create(layer, src, dsts)
+                for dn in dsts:
+                    fx.send(owner(dn), f"mc:{layer}:{src}:{dn}", fd, keep=True)
+                os.close(fd)
+    except Exception as e:                                  # noqa: BLE001
+        ok, why = False, f"create: {e}"
+    if not agreed(ok):
+        return False, why or "multicast object creation failed on another rank"
+    try:
+        for (layer, src, dsts) in groups:
+            for dn in dsts:
+                if owner(dn) == rank:
+                    eng.mcast_join(layer, src, dsts, dn, fx.recv(f"mc:{layer}:{src}:{dn}"))
+    except Exception as e:                                  # noqa: BLE001
+        ok, why = False, f"join: {e}"
+    if not agreed(ok):
+        return False, why or "joining the multicast object failed on another rank"
+    try:
+        for (layer, src, dsts) in groups:
+            if owner(src) == rank or any(owner(dn) == rank for dn in dsts):
+                eng.mcast_bind(layer, src, dsts)
+    except Exception as e:                                  # noqa: BLE001
+        ok, why = False, f"bind: {e}"
+    if not agreed(ok):
+        return False, why or "binding to the multicast object failed on another rank"
+    return True, ""

@@ -206,6 +206,15 @@ int dissem_plan_directions(dissem_xfer *xfers, int n, const int *gpu_of_node, in
  * dissem_plan_optimize applies it first.  Pure host logic. */
 int dissem_plan_align(dissem_xfer *xfers, int n, int *n_out);
 
+/* Several nodes on one GPU (the 1-, 2- and 4-GPU runs of an 8-node config).  The reference's planners know nodes, not
+ * GPUs: they may fetch a layer over NVLink although another node on the destination's own GPU holds it.  Given who holds
+ * which layer in HBM (holder_nodes[i] holds holder_layers[i], whole), every transfer that crosses GPUs while a holder
+ * shares the destination's GPU is re-sourced from that holder (an HBM-local copy, ~8x the link rate, and no port load);
+ * touching fragments that end up with the same source are merged.  In place; *n_out = transfers left (the order
+ * changes: sorted by destination, layer, source, offset).  The delivered store is unchanged.  Pure host logic. */
+int dissem_plan_localize(dissem_xfer *xfers, int n, const int *gpu_of_node, int n_nodes, const int *holder_nodes,
+                         const int *holder_layers, int n_holders, int *n_out);
+
 /* Relay / pipelined forwarding (generalises the reference's tee-pipe, transport.go:145-196, and mode 1's peer
  * retransmission, node.go:1462-1484, to piece granularity).  Rewrites a plan: transfers of the same bytes from one
  * source to k destinations become a chain  source -> d0 -> d1 -> ...  cut into `pieces` pieces (boundaries at multiples

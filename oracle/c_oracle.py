@@ -28,6 +28,10 @@ def lib() -> ctypes.CDLL:
         _LIB = ctypes.CDLL(path)
         _LIB.oracle_fill.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_int64, ctypes.c_uint64, ctypes.c_void_p]
         _LIB.oracle_checksum.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]
+        _LIB.oracle_fill_range.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_int64, ctypes.c_int64, ctypes.c_uint64,
+                                           ctypes.c_void_p]
+        _LIB.oracle_fill_checksum.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_int64, ctypes.c_uint64, ctypes.c_int64,
+                                              ctypes.c_void_p]
         _LIB.oracle_tcp_run.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(OracleXfer),
                                         ctypes.c_int, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int,
                                         ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]
@@ -54,6 +58,37 @@ def checksum(data: np.ndarray, chunk_bytes: int = 256 * 1024) -> np.ndarray:
     if rc != 0:
         raise ValueError("oracle_checksum failed")
     return out
+
+
+def fill_range(kind: int, layer_id: int, off: int, length: int, seed: int = 0) -> np.ndarray:
+    """fill_bytes(kind, layer_id, off + length, seed)[off:] for off % 8 == 0, without building the bytes before `off`."""
+    out = np.empty(max(length, 0), dtype=np.uint8)
+    rc = lib().oracle_fill_range(kind, layer_id, off, max(length, 0), seed & ((1 << 64) - 1), out.ctypes.data)
+    if rc != 0:
+        raise ValueError("oracle_fill_range failed (offset must be a multiple of 8)")
+    return out
+
+
+def fill_checksum(kind: int, layer_id: int, size: int, seed: int = 0, chunk_bytes: int = 256 * 1024) -> np.ndarray:
+    """checksum(fill_bytes(kind, layer_id, size, seed)) without building the layer in memory (one chunk at a time)."""
+    n_chunks = (max(size, 0) + chunk_bytes - 1) // chunk_bytes
+    out = np.zeros((n_chunks, 2), dtype=np.uint64)
+    rc = lib().oracle_fill_checksum(kind, layer_id, max(size, 0), seed & ((1 << 64) - 1), chunk_bytes, out.ctypes.data)
+    if rc != 0:
+        raise ValueError("oracle_fill_checksum failed")
+    return out
+
+
+def fill_checksum_many(kind: int, layers: Sequence[int], size: int, seed: int = 0, threads: int = 0) -> dict:
+    """{layer: fill_checksum(...)} computed on `threads` host threads (ctypes releases the GIL inside the C call)."""
+    from concurrent.futures import ThreadPoolExecutor
+    layers = list(layers)
+    if not layers:
+        return {}
+    threads = threads or min(len(layers), max(1, (os.cpu_count() or 2) // 2))
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        tabs = list(ex.map(lambda l: fill_checksum(kind, l, size, seed), layers))
+    return dict(zip(layers, tabs))
 
 
 def tcp_run(n_nodes: int, leader: int, xfers: Sequence, src_layers: Sequence[np.ndarray],

@@ -102,6 +102,72 @@ int oracle_checksum(const uint8_t *data, int64_t size, int64_t chunk_bytes, uint
     return 0;
 }
 
+/* Bytes [off, off+len) of the layer oracle_fill would write (off a multiple of 8), for spot checks of full-size layers. */
+int oracle_fill_range(int kind, uint64_t layer_id, int64_t off, int64_t len, uint64_t seed, uint8_t *out) {
+    if (off < 0 || len < 0 || off % 8) return -1;
+    if (kind == 0) { memset(out, 0, (size_t)len); return 0; }
+    if (kind == 2) { memset(out, 0xA5, (size_t)len); return 0; }
+    if (kind != 1) return -1;
+    const uint64_t base = seed + (layer_id + 1) * GOLDEN;
+    const int64_t w0 = off / 8, nfull = len / 8;
+    for (int64_t i = 0; i < nfull; ++i) {
+        uint64_t w = mix64(base + (uint64_t)(w0 + i));
+        memcpy(out + 8 * i, &w, 8);
+    }
+    if (len % 8) {
+        uint64_t w = mix64(base + (uint64_t)(w0 + nfull));
+        memcpy(out + 8 * nfull, &w, (size_t)(len % 8));
+    }
+    return 0;
+}
+
+/* The table oracle_checksum would give for the bytes oracle_fill would write, without materialising the layer:
+ * one chunk at a time through a chunk-sized buffer (full-size Llama-70B layers: 1.7 GB each, 80 of them).
+ * Same two definitions, composed; tests/test_oracle_golden.py checks the composition against the two calls. */
+int oracle_fill_checksum(int kind, uint64_t layer_id, int64_t size, uint64_t seed, int64_t chunk_bytes, uint64_t *out) {
+    if (size < 0 || chunk_bytes <= 0 || chunk_bytes % 8 || kind < 0 || kind > 2) return -1;
+    uint8_t *buf = (uint8_t *)malloc((size_t)chunk_bytes);
+    if (!buf) return -1;
+    const uint64_t base = seed + (layer_id + 1) * GOLDEN;
+    int64_t n_chunks = (size + chunk_bytes - 1) / chunk_bytes;
+    for (int64_t c = 0; c < n_chunks; ++c) {
+        int64_t b0 = c * chunk_bytes, b1 = b0 + chunk_bytes;
+        if (b1 > size) b1 = size;
+        const int64_t len = b1 - b0;
+        if (kind == 0) memset(buf, 0, (size_t)len);
+        else if (kind == 2) memset(buf, 0xA5, (size_t)len);
+        else {
+            const int64_t w0 = b0 / 8, nfull = len / 8;       /* chunk_bytes % 8 == 0: chunks start on a u64 word */
+            for (int64_t i = 0; i < nfull; ++i) {
+                uint64_t w = mix64(base + (uint64_t)(w0 + i));
+                memcpy(buf + 8 * i, &w, 8);
+            }
+            if (len % 8) {
+                uint64_t w = mix64(base + (uint64_t)(w0 + nfull));
+                memcpy(buf + 8 * nfull, &w, (size_t)(len % 8));
+            }
+        }
+        uint64_t A = 0, B = 0;
+        int64_t p = 0;
+        for (; p + 4 <= len; p += 4) {
+            uint32_t w;
+            memcpy(&w, buf + p, 4);
+            A += w;
+            B += ((uint64_t)((b0 + p) >> 2) + 1) * (uint64_t)w;
+        }
+        if (p < len) {
+            uint32_t w = 0;
+            memcpy(&w, buf + p, (size_t)(len - p));
+            A += w;
+            B += ((uint64_t)((b0 + p) >> 2) + 1) * (uint64_t)w;
+        }
+        out[2 * c] = A;
+        out[2 * c + 1] = B;
+    }
+    free(buf);
+    return 0;
+}
+
 /* ------------------------------------------------------------------------------------------
  * loopback TCP restatement
  * ------------------------------------------------------------------------------------------ */

@@ -313,6 +313,45 @@ def test_plan_align_moves_cuts_to_chunk_boundaries_and_keeps_coverage():
     assert rows == sorted([(0, 3, 0, C), (2, 3, C, 3 * C), (0, 4, 10, 20), (1, 4, 100, 20)])
 
 
+def test_plan_localize_takes_same_gpu_copies_and_reaches_the_best_sender_port_loads():
+    """BASELINE config 2 (ring placement) with its 8 nodes on 2 / 4 / 8 GPUs: after dissem_plan_localize + dissem_plan_optimize
+    the busiest NVLink port carries what the best sender choice allows (805 / 537 / 268 MB), and the
+    delivered store is the one the untouched flow plan delivers (oracle.apply_transfers on small layers)."""
+    text = o.config_stage_ring(8, 32, o.S2, ring=True)
+    p = d.plan(text, 3, time_scale=1_000_000)
+    xs = d.parse_plan(p)
+    holders = [(nd["id"], int(l)) for nd in p["nodes"] for l in nd["layers"]]
+    want = {2: 3 * 4 * o.S2, 4: 2 * 4 * o.S2, 8: 4 * o.S2}
+    for n_gpus, best in want.items():
+        g = [n % n_gpus for n in range(8)]
+        xo, _ = d.plan_optimize(d.plan_localize(xs, g, holders), g)
+        eg, ing = [0] * n_gpus, [0] * n_gpus
+        for x in xo:
+            assert (x.src_node, x.layer) in set(holders)
+            if g[x.src_node] != g[x.dst_node]:
+                eg[g[x.src_node]] += x.size
+                ing[g[x.dst_node]] += x.size
+        assert max(eg + ing) <= best + 2 * d.CHUNK_BYTES, (n_gpus, eg, ing)
+        assert sum(x.size for x in xo) == sum(x.size for x in xs)
+    # same store as the plain plan, byte for byte (small ragged layers so that the numpy oracle finishes at once)
+    small = o.config_stage_ring(8, 32, 3 * d.CHUNK_BYTES + 1234, ring=True)
+    ps = d.plan(small, 3, time_scale=1_000_000)
+    plain = d.parse_plan(ps)
+    hs = [(nd["id"], int(l)) for nd in ps["nodes"] for l in nd["layers"]]
+    g = [n % 2 for n in range(8)]
+    tuned, _ = d.plan_optimize(d.plan_localize(plain, g, hs), g)
+
+    def store_after(xfers):
+        st = {(n, l): o.fill_bytes(o.FILL_PATTERN, l, 3 * d.CHUNK_BYTES + 1234, 5) for (n, l) in hs}
+        o.apply_transfers(st, [o.Xfer(x.src_node, x.dst_node, x.layer, x.off, x.size, x.total) for x in xfers])
+        return st
+
+    a, b = store_after(plain), store_after(tuned)
+    assert set(a) == set(b)
+    for k in a:
+        assert (a[k] == b[k]).all(), k
+
+
 def test_plan_digests_are_stable():
     """Every BASELINE configuration x mode: the C++ planners still produce the committed plans (tests/golden/plan_digests.json),
     and the oracle agrees with each of them where it restates the mode."""

@@ -222,3 +222,23 @@ def test_tcp_restatement_disk_source_and_limit_rate(tmp_path):
     fast, _ = co.tcp_run(3, 0, xs[2:], [b], base_port=24300)
     paced, _ = co.tcp_run(3, 0, xs[2:], [b], base_port=24400, rates=[rate])
     assert want_s <= paced < want_s + 0.25 and fast < paced
+
+
+def test_streaming_oracle_helpers_compose_the_two_definitions():
+    """oracle_fill_checksum / oracle_fill_range (used on full-size layers by bench.py and the GPU tests) are the fill and the
+    checksum composed; pinned here against the plain calls and the numpy restatement on ragged sizes."""
+    import numpy as np
+    from oracle import c_oracle as co
+    for n in (0, 5, 262144, 262144 * 3 + 4321, 1_000_003):
+        for kind in (o.FILL_ZERO, o.FILL_PATTERN, o.FILL_POISON):
+            want = co.checksum(co.fill_bytes(kind, 7, n, 99))
+            assert np.array_equal(co.fill_checksum(kind, 7, n, 99), want), (n, kind)
+    n = 262144 * 3 + 4321
+    assert np.array_equal(co.fill_checksum(o.FILL_PATTERN, 7, n, 99), o.checksum(o.fill_bytes(o.FILL_PATTERN, 7, n, 99)))
+    whole = o.fill_bytes(o.FILL_PATTERN, 11, n, 5)
+    for off, ln in ((0, 100), (8, 4096), (262144, 262144), (n - 4321 + 1 - 1 - (n - 4321) % 8, 77), (n - 8 * 3, 24)):
+        off -= off % 8
+        ln = min(ln, n - off)
+        assert np.array_equal(co.fill_range(o.FILL_PATTERN, 11, off, ln, 5), whole[off:off + ln]), (off, ln)
+    many = co.fill_checksum_many(o.FILL_PATTERN, [1, 2, 3], 300000, 4, threads=2)
+    assert all(np.array_equal(many[l], o.checksum(o.fill_bytes(o.FILL_PATTERN, l, 300000, 4))) for l in (1, 2, 3))
