@@ -1910,7 +1910,7 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     std::string k(key);
     if (k == "ctas_per_sm") { if (value < 0 || value > 32) return set_error(DISSEM_EINVAL, "ctas_per_sm out of range"); ctx->opt_ctas_per_sm = value; }
     else if (k == "variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "variant must be 0 or 1"); ctx->opt_variant = value; }
-    else if (k == "tma_cfg") { if (value < 0 || value > 5) return set_error(DISSEM_EINVAL, "tma_cfg must be 0..5"); ctx->opt_tma_cfg = value; }
+    else if (k == "tma_cfg") { if (value < 0 || value > 8) return set_error(DISSEM_EINVAL, "tma_cfg must be 0..8"); ctx->opt_tma_cfg = value; }
     else if (k == "alloc_vmm") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0, 1 or 2"); ctx->opt_alloc_vmm = value; }
     else if (k == "mcast") { if (value < 0 || value > 3) return set_error(DISSEM_EINVAL, "mcast must be 0..3"); ctx->opt_mcast = value; }
     else if (k == "pull") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "pull must be 0, 1 or 2"); ctx->opt_pull = value; }

@@ -26,6 +26,15 @@ __device__ __forceinline__ uint4 ld_stream(const uint4 *p) {
                  : "l"(p));
     return r;
 }
+// A multicast unit rewrites the source's own copy through the multicast object while it is being read (the source is a
+// member): not read-only for the kernel's lifetime, so no .nc path for it.
+__device__ __forceinline__ uint4 ld_plain(const uint4 *p) {
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
 __device__ __forceinline__ void st_stream(uint4 *p, const uint4 &v) {
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
                  "r"(v.z), "r"(v.w)
@@ -172,8 +181,13 @@ copy_csum_kernel(const XferDesc *__restrict__ descs, int n_descs, long long tota
         // full tiles: kUnroll independent 16-byte loads in flight per thread, then the stores
         for (; v + (long long)(kUnroll - 1) * kThreads < nvec; v += (long long)kUnroll * kThreads) {
             uint4 r[kUnroll];
+            if (mc) {
 #pragma unroll
-            for (int j = 0; j < kUnroll; ++j) r[j] = ld_stream(s4 + v + j * kThreads);
+                for (int j = 0; j < kUnroll; ++j) r[j] = ld_plain(s4 + v + j * kThreads);
+            } else {
+#pragma unroll
+                for (int j = 0; j < kUnroll; ++j) r[j] = ld_stream(s4 + v + j * kThreads);
+            }
             if (d4) {
                 if (mc) {
 #pragma unroll
@@ -187,7 +201,7 @@ copy_csum_kernel(const XferDesc *__restrict__ descs, int n_descs, long long tota
             for (int j = 0; j < kUnroll; ++j) acc.vec(r[j], k_body + 4u * (unsigned int)(v + j * kThreads));
         }
         for (; v < nvec; v += kThreads) {
-            const uint4 r = ld_stream(s4 + v);
+            const uint4 r = mc ? ld_plain(s4 + v) : ld_stream(s4 + v);
             if (d4) { if (mc) st_multicast(d4 + v, r); else st_stream(d4 + v, r); }
             acc.vec(r, k_body + 4u * (unsigned int)v);
         }

@@ -16,8 +16,9 @@ namespace {
 
 // Ring shape is a template parameter: kStageBytes per bulk copy, kStages slots, kStoreLag bulk-store groups allowed in
 // flight before a stage is retired (needs kStoreLag + 2 <= kStages).
-constexpr int kConsumerWarps = 4;
-constexpr int kThreadsTma = 64 + 32 * kConsumerWarps;
+// kCW consumer warps per CTA is a template parameter too: 4 are enough to checksum tiles at HBM speed; multicast units,
+// whose stores are issued by the consumers (multimem.st from registers), get wider CTAs (see launch_copy_csum_tma).
+constexpr int kMaxConsumerWarps = 14;
 
 enum : int { kMetaLast = 1, kMetaEnd = 2 };
 
@@ -39,7 +40,7 @@ struct __align__(128) SmemLayout {
     unsigned char data[kStages][kStageBytes];
     StageMeta meta[kStages];
     unsigned long long usum[kStages][2];
-    unsigned long long red[2][2][kConsumerWarps];
+    unsigned long long red[2][2][kMaxConsumerWarps];
     unsigned long long full[kStages];
     unsigned long long empty[kStages];
     unsigned long long cons_done[kStages];
@@ -103,12 +104,13 @@ __device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
     return v;
 }
 
-template <int kStageBytes, int kStages, int kStoreLag>
-__global__ void __launch_bounds__(kThreadsTma, 1)
+template <int kStageBytes, int kStages, int kStoreLag, int kConsumerWarps = 4>
+__global__ void __launch_bounds__(64 + 32 * kConsumerWarps, 2)
 copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long total_units, int unit_shift,
                      SchedCounters *counters) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     static_assert(kStoreLag + 2 <= kStages, "ring too shallow for the store lag");
+    static_assert(kConsumerWarps <= kMaxConsumerWarps, "red[] too small");
     using Smem = SmemLayout<kStageBytes, kStages>;
     Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -275,7 +277,26 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
             const int nvec = n >> 4;
             const bool mc = sm.meta[s].mc != 0 && sm.meta[s].dst != nullptr;
             uint4 *mcdst = mc ? reinterpret_cast<uint4 *>(sm.meta[s].dst + pos) : nullptr;
-            for (int v = ctid; v < nvec; v += kCThreads) {
+            int v = ctid;
+            if (mc) {
+                // multicast unit: the stores leave from registers.  Four tiles are read, their four multimem.st issued back
+                // to back, and only then folded into the checksum, so that a thread keeps several stores in flight.
+                for (; v + 3 * kCThreads < nvec; v += 4 * kCThreads) {
+                    uint4 w[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) w[j] = tile[v + j * kCThreads];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) st_multicast16(mcdst + v + j * kCThreads, w[j]);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const unsigned int k0 = k_stage + 4u * (unsigned int)(v + j * kCThreads);
+                        a += (unsigned long long)w[j].x + w[j].y + w[j].z + w[j].w;
+                        s2 += (unsigned long long)k0 * w[j].x + (unsigned long long)(k0 + 1) * w[j].y +
+                              (unsigned long long)(k0 + 2) * w[j].z + (unsigned long long)(k0 + 3) * w[j].w;
+                    }
+                }
+            }
+            for (; v < nvec; v += kCThreads) {
                 const uint4 w = tile[v];
                 if (mc) st_multicast16(mcdst + v, w);
                 const unsigned int k0 = k_stage + 4u * (unsigned int)v;
@@ -305,12 +326,13 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
     }
 }
 
-template <int kStageBytes, int kStages, int kStoreLag>
+template <int kStageBytes, int kStages, int kStoreLag, int kConsumerWarps = 4>
 static cudaError_t launch_tma(const XferDesc *descs, int n_descs, long long total_units, int unit_shift,
                               SchedCounters *counters, const LaunchCfg &cfg, cudaStream_t stream, int *grid_out) {
     using Smem = SmemLayout<kStageBytes, kStages>;
     static_assert(sizeof(Smem) <= 112 * 1024, "two CTAs per SM");
-    auto kern = copy_csum_tma_kernel<kStageBytes, kStages, kStoreLag>;
+    auto kern = copy_csum_tma_kernel<kStageBytes, kStages, kStoreLag, kConsumerWarps>;
+    constexpr int kThreadsTma = 64 + 32 * kConsumerWarps;
     const int smem = (int)sizeof(Smem) + 128;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
@@ -343,6 +365,10 @@ cudaError_t launch_copy_csum_tma(const XferDesc *descs, int n_descs, long long t
         case 3: return launch_tma<16384, 4, 2>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
         case 4: return launch_tma<8192, 6, 3>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
         case 5: return launch_tma<4096, 12, 6>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        // wider CTAs (8 / 14 consumer warps): the shapes for multicast units, whose stores the consumers issue
+        case 6: return launch_tma<16384, 6, 3, 8>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 7: return launch_tma<16384, 6, 3, 14>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
+        case 8: return launch_tma<8192, 6, 3, 14>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
         default: return launch_tma<16384, 6, 3>(descs, n_descs, total_units, unit_shift, counters, cfg, stream, grid_out);
     }
 }

@@ -448,6 +448,45 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
                 ++checked;
             }
     }
+    // "dump_tables": the raw evidence of every assigned (node, layer) — fused checksum table, received counter, first and
+    // last 4 KiB — so that a caller can hold the run against its own oracle instead of trusting `verified` above, which
+    // only compares values this library computed with each other.
+    Json tables = Json::array();
+    if (opt_i("dump_tables", 0) != 0) {
+        auto hex = [](const uint8_t *p, size_t n) {
+            static const char *digits = "0123456789abcdef";
+            std::string h(2 * n, '0');
+            for (size_t i = 0; i < n; ++i) { h[2 * i] = digits[p[i] >> 4]; h[2 * i + 1] = digits[p[i] & 15]; }
+            return h;
+        };
+        for (auto &na : cfg.Assign)
+            for (auto &la : na.second) {
+                int64_t size = 0;
+                rc = dissem_layer_info(ctx, (int)na.first, (int)la.first, &size, nullptr);
+                if (rc) return set_error(DISSEM_EPLAN, "node %u ended without layer %u", na.first, la.first);
+                const int64_t nc = (size + DISSEM_CHUNK_BYTES - 1) / DISSEM_CHUNK_BYTES;
+                std::vector<uint64_t> fused((size_t)std::max<int64_t>(2 * nc, 1));
+                rc = dissem_layer_checksums(ctx, (int)na.first, (int)la.first, fused.data(), nc);
+                if (rc) return rc;
+                int64_t rcv = 0;
+                rc = dissem_layer_received(ctx, (int)na.first, (int)la.first, &rcv);
+                if (rc) return rc;
+                const int64_t edge = std::min<int64_t>(size, 4096);
+                std::vector<uint8_t> head((size_t)std::max<int64_t>(edge, 1)), tail((size_t)std::max<int64_t>(edge, 1));
+                rc = dissem_layer_read(ctx, (int)na.first, (int)la.first, head.data(), 0, edge);
+                if (!rc) rc = dissem_layer_read(ctx, (int)na.first, (int)la.first, tail.data(), size - edge, edge);
+                if (rc) return rc;
+                Json t = Json::object();
+                t.set("node", Json::of((int64_t)na.first));
+                t.set("layer", Json::of((int64_t)la.first));
+                t.set("size", Json::of(size));
+                t.set("received", Json::of(rcv));
+                t.set("fused", Json::of(hex(reinterpret_cast<const uint8_t *>(fused.data()), (size_t)nc * 16)));   // little-endian (A, B) pairs
+                t.set("head", Json::of(hex(head.data(), (size_t)edge)));
+                t.set("tail", Json::of(hex(tail.data(), (size_t)edge)));
+                tables.push(std::move(t));
+            }
+    }
     Json out = Json::object();
     out.set("mode", Json::of((int64_t)mode));
     out.set("batched", Json::boolean(batched));
@@ -472,6 +511,7 @@ int dissem_run_json(const char *config_json_text, int mode, const int *node_devi
         xs.push(std::move(r));
     }
     out.set("xfers", std::move(xs));
+    if (opt_i("dump_tables", 0) != 0) out.set("tables", std::move(tables));
     *json_out = dup_cstr(out.dump());
     return *json_out ? DISSEM_OK : set_error(DISSEM_ENOMEM, "out of memory");
 }

@@ -11,7 +11,7 @@
 #include "../../include/dissem_host.h"
 
 int main(int argc, char **argv) {
-    int id = -1, mode = -1, verbose = 0, batched = 0, gpus = 1, pace = 0;
+    int id = -1, mode = -1, verbose = 0, batched = 0, gpus = 1, pace = 0, dump_tables = 0;
     std::string file, storage;
     bool save_disk = false;
     long long time_scale = 1000000;
@@ -27,6 +27,7 @@ int main(int argc, char **argv) {
         else if (a == "-v") verbose = 1;
         else if (a == "--batched") batched = 1;
         else if (a == "--pace") pace = 1;                             // honour LimitRate as writeWithLimit does (transport.go:407-424)
+        else if (a == "--dump-tables") dump_tables = 1;              // with -v: the report carries every delivered layer's table and edge bytes
         else if (a == "--gpus") gpus = atoi(next());
         else if (a == "--time-scale") time_scale = atoll(next());
     }
@@ -44,7 +45,7 @@ int main(int argc, char **argv) {
     int devs[4096];
     for (int i = 0; i < 4096; ++i) devs[i] = i % gpus;
     std::string opts = "{\"batched\":" + std::to_string(batched) + ",\"time_scale\":" + std::to_string(time_scale) +
-                       ",\"flags\":3,\"seed\":24301,\"pace\":" + std::to_string(pace);
+                       ",\"flags\":3,\"seed\":24301,\"pace\":" + std::to_string(pace) + ",\"dump_tables\":" + std::to_string(dump_tables);
     if (save_disk) {
         std::string esc;
         for (char ch : storage) { if (ch == '"' || ch == '\\') esc += '\\'; esc += ch; }

@@ -44,7 +44,7 @@ void dissem_free(void *p);
  * in-process Transport whose layer branch is the device engine.  Needs a GPU.
  * node_device[i]: CUDA ordinal for the config's i-th node (NULL = all on device 0).
  * opts_json (may be NULL): {"seed":S,"policy":P,"time_scale":T,"flags":F,"fill":K,"batched":bool,"verify":bool,
- *                           "storage":"<path>","pace":bool,"reserve":bool}
+ *                           "storage":"<path>","pace":bool,"reserve":bool,"dump_tables":bool}
  *   batched=false: one Transport.Send per layerMsg, as the reference issues them;
  *   batched=true : the leader hands the whole plan to dissem_schedule_submit (one launch per source GPU);
  *   storage      : the `-s` flag (cmd/main.go:17, :93-101): every node's initial layers are files
@@ -52,7 +52,10 @@ void dissem_free(void *p);
  *                  with the run's fill) attached with dissem_layer_attach_file and sent as DiskLayer sources;
  *   reserve      : (default true) receive buffers for the Assignment are set aside with dissem_layer_reserve before the
  *                  clock starts; false leaves their allocation inside each send, where the reference has it;
- *   pace         : unbatched layer sends honour LayerSrc.Meta.LimitRate as writeWithLimit does (dissem_pace_schedule).
+ *   pace         : unbatched layer sends honour LayerSrc.Meta.LimitRate as writeWithLimit does (dissem_pace_schedule);
+ *   dump_tables  : the report gains "tables": one entry per assigned (node, layer) with its size, received counter, fused
+ *                  checksum table and first / last 4 KiB as hex strings — the evidence a caller needs to check the run
+ *                  against an oracle of its own ("verified" only compares values this library computed with each other).
  * *json_out: {"time_to_deliver_ms":..,"device_ms":..,"bytes":..,"n_xfers":..,"acks":..,"verified":bool,...} */
 int dissem_run_json(const char *config_json, int mode, const int *node_device, const char *opts_json,
                     char **json_out);

@@ -11,6 +11,7 @@ import pytest
 
 import dissem_b200 as d
 from oracle import dissem_oracle as o
+from roles_oracle import check_against_oracle, run_checked
 
 pytestmark = pytest.mark.gpu
 host = importlib.import_module("distributed-llm-dissemination_b200.host")
@@ -156,9 +157,9 @@ def test_distribution_from_disk_layers(tmp_path, mode, batched):
     l0 = sorted(leader.layers)[0]
     odd = o.fill_bytes(o.FILL_PATTERN, 1000 + l0, size, SEED + 1)
     o.create_disk_layer(str(tmp_path), leader.id, l0, size, contents=odd)
-    r = host.run_distribution(text, mode, batched=batched, seed=SEED, time_scale=1_000_000, flags=3, timeout_ms=20000,
-                              storage=str(tmp_path))
-    assert r["verified"] and r["ready_equals_assignment"] and r["layers_checked"] > 0
+    r = run_checked(text, mode, batched=batched, seed=SEED, time_scale=1_000_000, flags=3, timeout_ms=20000,
+                    storage=str(tmp_path), overrides={(leader.id, l0): odd})
+    assert r["oracle_checked"] > 0 and r["ready_equals_assignment"] and r["layers_checked"] > 0
     for n in cfg.nodes:
         for layer, (sz, _) in n.layers.items():
             p = o.disk_layer_path(str(tmp_path), n.id, layer)
@@ -175,10 +176,11 @@ def test_cli_storage_flag(tmp_path):
         pytest.skip("CLI not built")
     cfg = os.path.join(root, "tests", "data", "cli_config_4x8.json")
     for mode, extra in (("1", []), ("2", []), ("3", ["--pace"]), ("0", ["--batched"])):
-        r = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", mode, "-s", str(tmp_path), "-v"] + extra, capture_output=True, text=True, timeout=180)
+        r = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", mode, "-s", str(tmp_path), "-v", "--dump-tables"] + extra, capture_output=True, text=True, timeout=180)
         assert r.returncode == 0, (mode, r.stderr)
         assert f"storagePath: {tmp_path}" in r.stdout and "Time to deliver: " in r.stdout
-        assert '"verified":true' in r.stdout and '"ready_equals_assignment":true' in r.stdout, (mode, r.stdout)
+        report = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+        assert report["ready_equals_assignment"] and check_against_oracle(open(cfg).read(), report, seed=24301) > 0, mode
     conf = o.parse_config(open(cfg).read())
     for n in conf.nodes:
         for layer, (sz, _) in n.layers.items():
@@ -195,9 +197,9 @@ def test_paced_sends_honour_limit_rate(mode):
         n["Sources"] = {k: rate for k in n["Sources"]}
     text = json.dumps(conf)
     floor_ms = o.limiter_write_times(size, rate)[-1][0] / 1e6            # 39.3 ms for one layer
-    fast = host.run_distribution(text, mode, seed=SEED, time_scale=1_000_000, flags=2, timeout_ms=20000)
-    paced = host.run_distribution(text, mode, seed=SEED, time_scale=1_000_000, flags=2, timeout_ms=20000, pace=1)
-    assert fast["verified"] and paced["verified"] and paced["ready_equals_assignment"]
+    fast = run_checked(text, mode, seed=SEED, time_scale=1_000_000, flags=2, timeout_ms=20000)
+    paced = run_checked(text, mode, seed=SEED, time_scale=1_000_000, flags=2, timeout_ms=20000, pace=1)
+    assert fast["oracle_checked"] == paced["oracle_checked"] == 4 and paced["ready_equals_assignment"]
     if mode == 3:
         # the flow plan's own rate: size * ticks-per-second / t, never above the source's limit
         floor_ms = o.limiter_write_times(size, min(rate, size * 1_000_000 // paced["t"]))[-1][0] / 1e6 * 0.98
@@ -246,9 +248,9 @@ def test_file_to_peer_gpu_and_disk_distribution_over_two_gpus(tmp_path):
     text = o.config_ring_fixture(4, 300_001)
     for mode, batched in ((1, False), (3, True)):
         store = tmp_path / f"m{mode}"
-        r = host.run_distribution(text, mode, node_device=[i % 2 for i in range(5)], batched=batched, seed=SEED,
-                                  time_scale=1_000_000, flags=3, timeout_ms=20000, storage=str(store))
-        assert r["verified"] and r["ready_equals_assignment"]
+        r = run_checked(text, mode, node_device=[i % 2 for i in range(5)], batched=batched, seed=SEED,
+                        time_scale=1_000_000, flags=3, timeout_ms=20000, storage=str(store))
+        assert r["oracle_checked"] > 0 and r["ready_equals_assignment"]
 
 
 def test_disk_layer_read_once_then_forwarded(tmp_path):
@@ -281,8 +283,8 @@ def test_batched_distribution_from_disk_with_fanout(tmp_path):
     conf["Assignment"] = {"1": {"1": {}, "2": {}}, "2": {"1": {}, "2": {}}, "3": {"1": {}, "3": {}}, "4": {"4": {}}}
     text = json.dumps(conf)
     for batched in (True, False):
-        r = host.run_distribution(text, 0, batched=batched, seed=SEED, timeout_ms=20000, storage=str(tmp_path / str(batched)))
-        assert r["verified"] and r["ready_equals_assignment"] and r["layers_checked"] == 7
+        r = run_checked(text, 0, batched=batched, seed=SEED, timeout_ms=20000, storage=str(tmp_path / str(batched)))
+        assert r["oracle_checked"] == 7 and r["ready_equals_assignment"] and r["layers_checked"] == 7
 
 
 def test_diskspeed_tool(tmp_path):

@@ -11,6 +11,7 @@ import pytest
 import dissem_b200 as d
 from oracle import c_oracle as co
 from oracle import dissem_oracle as o
+from roles_oracle import check_against_oracle, run_checked
 
 pytestmark = pytest.mark.gpu
 host = importlib.import_module("distributed-llm-dissemination_b200.host")
@@ -256,8 +257,8 @@ def test_reference_fixtures_through_roles(mode, fixture, batched):
     flags = host.PLAN_ZERO_RATE_UNLIMITED if fixture == "readme" else 0
     if mode == 3 and fixture == "readme":
         pytest.skip("README config has no NetworkBW")
-    r = host.run_distribution(text, mode, batched=batched, seed=SEED, time_scale=1_000_000, flags=flags, timeout_ms=10000)
-    assert r["ready_equals_assignment"] and r["verified"]
+    r = run_checked(text, mode, batched=batched, seed=SEED, time_scale=1_000_000, flags=flags, timeout_ms=10000)
+    assert r["ready_equals_assignment"] and r["oracle_checked"] == len({(x[1], x[2]) for x in r["xfers"]})
     cfg = o.parse_config(text)
     if mode == 0:
         want = o.plan_mode0(cfg)
@@ -273,12 +274,12 @@ def test_reference_fixtures_through_roles(mode, fixture, batched):
 @pytest.mark.parametrize("mode", [0, 1, 2, 3])
 def test_roles_move_real_layers(mode):
     text = o.config_stage_ring(4, 8, 3 * d.CHUNK_BYTES + 1001, ring=(mode in (1, 2)))
-    r = host.run_distribution(text, mode, batched=False, seed=SEED, time_scale=1_000_000, timeout_ms=20000)
-    assert r["verified"] and r["layers_checked"] == 6 and r["ready_equals_assignment"]
+    r = run_checked(text, mode, batched=False, seed=SEED, time_scale=1_000_000, timeout_ms=20000)
+    assert r["oracle_checked"] == 6 and r["layers_checked"] == 6 and r["ready_equals_assignment"]
     if mode == 2:
         return                      # the pull scheduler is message-driven by construction: no batched form
-    rb = host.run_distribution(text, mode, batched=True, seed=SEED, time_scale=1_000_000, timeout_ms=20000)
-    assert rb["verified"] and rb["xfers"] == r["xfers"] and rb["launches"] == 2
+    rb = run_checked(text, mode, batched=True, seed=SEED, time_scale=1_000_000, timeout_ms=20000)
+    assert rb["oracle_checked"] == 6 and rb["xfers"] == r["xfers"] and rb["launches"] == 2
 
 
 # ---- error behaviour ---------------------------------------------------------------------------------------
@@ -445,9 +446,9 @@ def test_roles_across_gpus(mode, batched):
     if n < 2:
         pytest.skip("needs 2 GPUs")
     text = o.config_stage_ring(4, 8, 3 * d.CHUNK_BYTES + 1001, ring=(mode in (1, 2)))
-    r = host.run_distribution(text, mode, node_device=[i % n for i in range(4)], batched=batched, seed=SEED,
-                              time_scale=1_000_000, timeout_ms=20000)
-    assert r["verified"] and r["ready_equals_assignment"] and r["layers_checked"] == 6
+    r = run_checked(text, mode, node_device=[i % n for i in range(4)], batched=batched, seed=SEED,
+                    time_scale=1_000_000, timeout_ms=20000)
+    assert r["oracle_checked"] == 6 and r["ready_equals_assignment"] and r["layers_checked"] == 6
 
 
 # ---- relay / pipelined forwarding over rounds ------------------------------------------------------
@@ -566,10 +567,11 @@ def test_cli_keeps_the_reference_surface():
     assert out.startswith("usage: -id 0 -f config.json -s . -m 2 -l -v")
     cfg = os.path.join(root, "tests", "data", "cli_config_4x8.json")
     for mode in ("0", "1", "2", "3"):
-        r = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", mode, "-v"], capture_output=True, text=True, timeout=120)
+        r = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", mode, "-v", "--dump-tables"], capture_output=True, text=True, timeout=120)
         assert r.returncode == 0, r.stderr
         assert "launching leader..." in r.stdout and "Time to deliver: " in r.stdout
-        assert '"verified":true' in r.stdout and '"ready_equals_assignment":true' in r.stdout
+        report = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+        assert report["ready_equals_assignment"] and check_against_oracle(open(cfg).read(), report, seed=24301) > 0
     bad = subprocess.run([exe, "-id", "0", "-f", cfg, "-m", "9"], capture_output=True, text=True, timeout=60)
     assert bad.returncode != 0 and "unknown mode" in bad.stderr
 
@@ -608,10 +610,10 @@ def test_mode3_multi_destination_through_roles():
     flags = host.PLAN_SIZES_FROM_ANNOUNCES | host.PLAN_MULTI_DEST
     n = max(1, min(_n_gpus(), 4))
     for batched in (False, True):
-        r = host.run_distribution(text, 3, node_device=[i % n for i in range(4)], batched=batched, seed=SEED,
-                                  time_scale=1_000_000, flags=flags, timeout_ms=20000)
-        assert r["verified"] and r["ready_equals_assignment"]
-        assert r["layers_checked"] == sum(len(v) for v in o.parse_config(text).assignment.values())
+        r = run_checked(text, 3, node_device=[i % n for i in range(4)], batched=batched, seed=SEED,
+                        time_scale=1_000_000, flags=flags, timeout_ms=20000)
+        assert r["ready_equals_assignment"]
+        assert r["oracle_checked"] == r["layers_checked"] == sum(len(v) for v in o.parse_config(text).assignment.values())
 
 
 def test_concurrent_sends_from_many_threads():
@@ -741,8 +743,8 @@ def test_reserved_destination_buffers():
         assert np.array_equal(eng.checksums(1, 2), o.checksum(want))
         assert eng.received(1, 2) == size
         eng.reserve(0, 1 << 20, 3)                             # left unused: released by close
-    r = host.run_distribution(o.config_ring_fixture(4, 300_001), 1, seed=SEED, timeout_ms=10000, reserve=0)
-    assert r["verified"] and r["ready_equals_assignment"]
+    r = run_checked(o.config_ring_fixture(4, 300_001), 1, seed=SEED, timeout_ms=10000, reserve=0)
+    assert r["oracle_checked"] == 4 and r["ready_equals_assignment"]
 
 
 @pytest.mark.parametrize("case", range(10))
@@ -792,3 +794,149 @@ def test_random_fragment_plans_match_oracle(case):
         for key, cs in landed.items():
             assert np.array_equal(eng.checksums(*key), cs), (case, key)
             assert eng.received(*key) == sum(x.size for x in oplan if (x.dst, x.layer) == key)
+
+
+# ---- round 2: relaunches of the full-size flow plan, cross-GPU ordering, the read-back path -------------------------
+@pytest.mark.parametrize("aligned", [False, True])
+def test_relaunching_the_64MiB_flow_plan_three_times(aligned):
+    """BASELINE config 2's flow.go plan at full size (28 destinations x 64 MiB, ~29 fragments) compiled once and launched
+    three times back to back: after every launch each fused table equals the C oracle's.  Raw cuts share checksum chunks
+    between senders (the compiler names an owner that re-zeroes them); dissem_plan_align removes the sharing."""
+    text = o.config_stage_ring(8, 32, o.S2)
+    cfg = o.parse_config(text)
+    xfers = d.parse_plan(d.plan(text, 3, time_scale=1_000_000))
+    if aligned:
+        xfers = d.plan_align(xfers)
+        assert all(x.off % d.CHUNK_BYTES == 0 for x in xfers)
+    dsts = sorted({(x.dst_node, x.layer) for x in xfers})
+    want = co.fill_checksum_many(o.FILL_PATTERN, sorted({l for _n, l in dsts}), o.S2, SEED)
+    two = _n_gpus() >= 2
+    with d.Engine([i % 2 if two else 0 for i in range(8)]) as eng:
+        _materialise(eng, cfg)
+        _alloc_destinations(eng, xfers)
+        s = eng.compile(xfers)
+        for k in range(3):
+            t = eng.launch(s)
+            if k == 1:
+                t2 = eng.launch(s)                 # two launches in flight at once: the second must not wipe the first's sums
+                eng.wait(t)
+                t = t2
+            eng.wait(t)
+            got = eng.checksums_many(dsts)
+            for g, (n, l) in zip(got, dsts):
+                assert np.array_equal(g, want[l]), f"launch {k}: table of layer {l} at node {n} differs from the oracle"
+        eng.sched_free(s)
+
+
+def test_checksums_many_and_ticket_release():
+    """dissem_layers_checksums returns what dissem_layer_checksums returns per layer (and the oracle's tables); a ticket
+    that was only ever polled is released with dissem_ticket_release, more often than the descriptor pool has slots."""
+    sizes = {1: 5 * d.CHUNK_BYTES + 77, 2: 1, 3: d.CHUNK_BYTES, 4: 3 * d.CHUNK_BYTES - 1}
+    two = _n_gpus() >= 2
+    with d.Engine([0, 1 if two else 0]) as eng:
+        for l, sz in sizes.items():
+            eng.alloc(0, l, sz)
+            eng.fill(0, l, d.FILL_PATTERN, SEED)
+            eng.alloc(1, l, sz)
+            eng.fill(1, l, d.FILL_POISON)
+        import time
+        for rep in range(300):                     # > 256 pool slots: polled tickets give their slot back
+            l = 1 + rep % 4
+            t = eng.send(0, 1, l, 0, sizes[l], sizes[l])
+            while not eng.poll(t):
+                time.sleep(0)
+            eng.release(t)
+            with pytest.raises(d.DissemError):
+                eng.wait(t)                         # released: gone
+        pairs = [(1, l) for l in sizes] + [(0, 1)]
+        many = eng.checksums_many(pairs)
+        for got, (n, l) in zip(many, pairs):
+            assert np.array_equal(got, eng.checksums(n, l))
+            if n == 1:
+                assert np.array_equal(got, o.checksum(o.fill_bytes(o.FILL_PATTERN, l, sizes[l], SEED)))
+        assert not many[-1].any()                   # a source's own table was never accumulated into
+        assert eng.checksums_many([]) == []
+
+
+def test_push_waits_for_the_destination_gpus_own_stream():
+    """Streams of different GPUs are not ordered by themselves.  GPU 1's stream is kept busy with local copies; a layer is
+    then allocated on GPU 1 (its trailer zeroing queues BEHIND that work) and GPU 0 pushes into it at once.  The push
+    must wait for the zeroing (the buffer's ready event): counter and table are exact afterwards, every time."""
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    big, size = 512 << 20, 9 * d.CHUNK_BYTES + 4321
+    want = o.fill_bytes(o.FILL_PATTERN, 7, size, SEED)
+    with d.Engine([0, 1, 1]) as eng:
+        eng.alloc(0, 7, size)
+        eng.fill(0, 7, d.FILL_PATTERN, SEED)
+        for l in (50, 51):
+            eng.alloc(1, l, big)
+            eng.fill(1, l, d.FILL_PATTERN, SEED)
+            eng.alloc(2, l, big)
+        busy = eng.compile([(1, 2, 50, 0, big, big), (1, 2, 51, 0, big, big)])       # HBM-local on GPU 1, ~0.33 ms a launch
+        eng.reserve(1, size, 8)                       # so that the allocation below does not synchronise the device
+        eng.wait(eng.launch(busy))
+        for rep in range(8):
+            tickets = [eng.launch(busy) for _ in range(12)]                         # ~4 ms of queued work on GPU 1's stream
+            eng.alloc(1, 100 + rep, size)             # trailer memset queued behind it
+            t = eng.send(0, 1, 100 + rep, 0, size, size)
+            eng.wait(t)
+            for b in tickets:
+                eng.wait(b)
+            assert eng.received(1, 100 + rep) == size, rep
+            assert np.array_equal(eng.checksums(1, 100 + rep), o.checksum(want)), rep
+            assert np.array_equal(eng.read(1, 100 + rep), want), rep
+        # the same for a PULL whose source is still being uploaded on the other GPU's stream
+        host_copy = o.fill_bytes(o.FILL_PATTERN, 8, size, SEED + 1)
+        eng.alloc(0, 8, size)
+        eng.alloc(1, 8, size)
+        for rep in range(4):
+            tickets = [eng.launch(busy) for _ in range(12)]
+            eng.fill(0, 8, d.FILL_POISON)
+            eng.write(0, 8, host_copy)                # queued on GPU 0's stream
+            eng.wait(eng.submit([d.Xfer(0, 1, 8, d.XFER_PULL, 0, size, size)]))      # executed by GPU 1
+            for b in tickets:
+                eng.wait(b)
+            assert np.array_equal(eng.read(1, 8), host_copy), rep
+        eng.sched_free(busy)
+
+
+def test_a_blocked_table_read_does_not_hold_up_other_senders():
+    """The reference calls Send from one goroutine per transfer (node.go:343).  One thread waits in
+    dissem_layer_checksums for a long batch to finish; another thread's dissem_send must still be accepted at once (the
+    read path does not hold the context's lock while it waits)."""
+    import threading
+    import time
+    big = 1 << 30
+    with d.Engine([0, 0, 0, 0]) as eng:
+        for l in (1, 2):
+            eng.alloc(0, l, big)
+            eng.fill(0, l, d.FILL_PATTERN, SEED)
+            eng.alloc(1, l, big)
+        eng.alloc(2, 9, 4096)
+        eng.fill(2, 9, d.FILL_PATTERN, SEED)
+        eng.alloc(3, 9, 4096)
+        s = eng.compile([(0, 1, 1, 0, big, big), (0, 1, 2, 0, big, big)])           # ~0.65 ms a launch
+        eng.wait(eng.launch(s))
+        tickets = [eng.launch(s) for _ in range(100)]                               # ~65 ms of queued work
+        blocked = {}
+
+        def reader():
+            t0 = time.perf_counter()
+            eng.checksums(1, 1)                      # waits for everything queued above
+            blocked["s"] = time.perf_counter() - t0
+
+        th = threading.Thread(target=reader)
+        th.start()
+        time.sleep(0.005)                            # the reader is inside the call now
+        t0 = time.perf_counter()
+        tk = eng.send(2, 3, 9, 0, 4096, 4096)
+        accept_s = time.perf_counter() - t0
+        th.join()
+        eng.wait(tk)
+        for t in tickets:
+            eng.wait(t)
+        assert blocked["s"] > 0.02, blocked          # the reader really was waiting on the GPU
+        assert accept_s < blocked["s"] / 2, (accept_s, blocked)
+        assert np.array_equal(eng.read(3, 9), o.fill_bytes(o.FILL_PATTERN, 9, 4096, SEED))
+        eng.sched_free(s)
