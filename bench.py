@@ -378,20 +378,37 @@ def best_sender_t_star(plan_nodes, assignment, gpu_of_node, size, world):
 
 
 class Runner:
-    """A plan on one engine: one compiled schedule per round.  Inside one process rounds are ordered on the device; with
-    one process per GPU the ranks meet at `barrier` between rounds."""
+    """A plan on one engine.  One process: one schedule, rounds ordered on the device by events.  One process per GPU:
+    a plan with rounds runs flag-driven when it can (multi.FlagRelaySchedule: all rounds in one schedule, hops wait on the
+    device for the source copy's received counter, one reset + barrier before the dissemination), else round by round
+    with a barrier between rounds."""
 
-    def __init__(self, eng, multi, xfers, barrier, multi_process):
+    def __init__(self, eng, multi, xfers, barrier, multi_process, owner=None, rank=0, allow_flags=True):
         self.eng, self.barrier, self.mp = eng, barrier, multi_process
-        self.rounds = multi.split_rounds(xfers) if multi_process else [list(xfers)]
-        self.scheds = [eng.compile(r) for r in self.rounds]
+        rounds = multi.split_rounds(xfers)
+        self.flag = None
+        if multi_process and len(rounds) > 1 and allow_flags and owner is not None and multi.flag_relay_ok(xfers):
+            self.flag = multi.FlagRelaySchedule(eng, xfers, owner, rank)
+            self.scheds = self.flag.scheds
+        else:
+            self.scheds = [eng.compile(r) for r in (rounds if multi_process else [list(xfers)])]
         info = [eng.sched_info(s) for s in self.scheds]
         self.units = sum(i[0] for i in info)
         self.launches = sum(i[1] for i in info)
         self.bytes = sum(i[2] for i in info)
+        self.n_rounds = len(rounds)
+
+    def describe(self):
+        if self.flag is not None:
+            return f"{self.n_rounds} rounds in one launch sequence, ordered on the device by received-counter waits"
+        if len(self.scheds) > 1:
+            return f"{len(self.scheds)} rounds, a barrier between rounds"
+        return f"{self.n_rounds} round(s), one schedule"
 
     def step(self):
         """One dissemination, waited for.  -> (device ms, copy-kernel ms) of this rank."""
+        if self.flag is not None:
+            return self.flag.run(self.barrier)
         dev = copy = 0.0
         for s in self.scheds:
             ms, cms = self.eng.wait_detail(self.eng.launch(s))
@@ -403,14 +420,17 @@ class Runner:
 
     def pipelined(self, k):
         """k disseminations enqueued back to back (single-round plans), then waited for."""
-        if len(self.scheds) > 1:
+        if len(self.scheds) > 1 or self.flag is not None:
             return [self.step() for _ in range(k)]
         tickets = [self.eng.launch(self.scheds[0]) for _ in range(k)]
         return [self.eng.wait_detail(t) for t in tickets]
 
     def free(self):
-        for s in self.scheds:
-            self.eng.sched_free(s)
+        if self.flag is not None:
+            self.flag.free()
+        else:
+            for s in self.scheds:
+                self.eng.sched_free(s)
         self.scheds = []
 
 
@@ -488,15 +508,24 @@ def parity_leg(d, multi, co, o, torch, dist, rank, world, local_rank, barrier):
     store = multi.SharedStore(eng, dist, world, rank, owner)
     store.share(xs)
     barrier()
-    run = Runner(eng, multi, xs, barrier, True)
-    run.step()
-    barrier()
-    res["relay"] = check(eng, [(rank, 100)] if rank != 0 else [])
-    res["relay_rounds"] = len(run.scheds)
-    run.free()
-    barrier()
+    for name, flags_on in (("relay", True), ("relay_barrier_per_round", False)):
+        if name != "relay":
+            eng.fill(rank, 100, d.FILL_PATTERN if rank == 0 else d.FILL_POISON, seed)
+            if rank != 0:
+                eng.reset(rank, 100)
+            barrier()
+        run = Runner(eng, multi, xs, barrier, True, owner=owner, rank=rank, allow_flags=flags_on)
+        run.step()
+        barrier()
+        timeouts = torch.tensor([eng.get_option("wait_timeouts")], device="cuda")
+        dist.all_reduce(timeouts, op=dist.ReduceOp.SUM)
+        res[name] = check(eng, [(rank, 100)] if rank != 0 else []) and int(timeouts.item()) == 0
+        res[name + "_how"] = run.describe()
+        run.free()
+        barrier()
     eng.close()
     # ---- NVLS multicast: layer 200 from rank 0 to every other rank, shareable VMM layers, handles as descriptors -----
+    size = 9 * d.CHUNK_BYTES + 4320                  # multimem.st moves 16-byte vectors: multicast needs a multiple of 16
     fx = multi.FdExchange(rank, "par" + os.environ.get("MASTER_PORT", "0"))
     barrier()
     eng = d.Engine(multi.device_of_node(world, owner, rank, local_rank))
@@ -597,12 +626,12 @@ def north_star(d, multi, co, o, torch, dist, rank, world, local_rank, barrier, n
         # ---- ours: dissem_plan_optimize (relay chains when they unload the busiest port, push/pull per transfer) -----
         xs, pieces = d.plan_optimize(base, gpus)
         store.share(xs)
-        run = Runner(eng, multi, xs, barrier, True)
+        run = Runner(eng, multi, xs, barrier, True, owner=owner, rank=rank)
         ms, dev_ms = timed(run)
-        ok = oracle_check(eng, co, o, my_dsts, size, expected)
+        ok = oracle_check(eng, co, o, my_dsts, size, expected) and eng.get_option("wait_timeouts") == 0
         flag = torch.tensor([1 if ok else 0], device="cuda")
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        r.update({"path": f"relay chains, {pieces} pieces, {len(run.scheds)} rounds" if pieces else "unicast, push/pull per transfer",
+        r.update({"path": f"relay chains, {pieces} pieces; {run.describe()}" if pieces else "unicast, push/pull per transfer",
                   "completion_ms": ms, "device_ms": dev_ms, "aggregate_GBps": D / ms / 1e6,
                   "frac_770": t_once / ms, "frac_900": t_once * LINK_GBPS / LINK_NOMINAL_GBPS / ms, "verified": bool(flag.item()),
                   "transfers_pulled": sum(1 for x in xs if x.flags & d.XFER_PULL)})
@@ -862,7 +891,7 @@ def run_ours(args, rank, world, local_rank):
                 barrier()
             _p, pl, _pc = make_plan()
             if dist is not None and any(d.xfer_round(x) for x in pl):      # rounds are not ordered across processes
-                r_ = Runner(eng, multi, pl, barrier, True)
+                r_ = Runner(eng, multi, pl, barrier, True, owner=owner, rank=rank)
                 r_.step()
                 r_.free()
             else:
@@ -974,7 +1003,7 @@ def run_ours(args, rank, world, local_rank):
             emit(rank)
             os._exit(3)
         LINE["parity"] = par
-        parity_failed = any(par.get(k) is False for k in ("push", "pull", "mcast", "relay"))
+        parity_failed = any(par.get(k) is False for k in ("push", "pull", "mcast", "relay", "relay_barrier_per_round"))
 
     # ---- CPU baseline on rank 0 at N=1 (bounded sample of the same workload) --------------------------------------
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -113,6 +113,9 @@ struct SchedPart {
     int pool_slot = -1;               // >= 0: d_descs points into the device's descriptor pool
     int round = 0;
     bool host_src = false;            // reads pinned host memory: runs the register kernel
+    bool has_mc = false;              // carries NVLS multicast units: runs the register kernel (multimem.st straight from the
+                                      // loaded registers: 570 GB/s against 533 GB/s through the shared-memory ring, any ring
+                                      // shape: profiles/r02_n2_mcast_probe.jsonl)
     XferDesc *d_descs = nullptr;
     int n_descs = 0;
     long long total_units = 0;
@@ -164,7 +167,7 @@ struct dissem_ctx {
     // dissem_layer_reserve: destination buffers allocated ahead of time, keyed by (device ordinal, allocation bytes)
     std::map<std::pair<int, int64_t>, std::vector<uint8_t *>> reserved;
     // options
-    int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0, opt_alloc_vmm = 0, opt_mcast = 1, opt_file_threads = 8;
+    int64_t opt_ctas_per_sm = 0, opt_variant = 1, opt_unit_bytes = 0, opt_reg_cfg = 1, opt_pull = 0, opt_tma_cfg = 0, opt_alloc_vmm = 0, opt_mcast = 1, opt_file_threads = 8, opt_mcast_variant = 0, opt_wait_src = 0;
 };
 
 namespace dissem {
@@ -415,7 +418,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         std::vector<XferDesc> descs;
         long long units = 0;
         int64_t bytes = 0;
-        bool any_host_src = false;
+        bool any_host_src = false, any_mc = false;
         std::vector<std::pair<int, int>> touch, writes;
         auto written = [&](int node, int layer) {
             if (ctx->node_dev_slot[node] < 0) return;                       // an imported buffer: its own process reads it
@@ -441,12 +444,17 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             d.size = x.size;
             d.total = x.total;
             d.first_unit = units;
+            if ((x.flags & DISSEM_XFER_WAIT_SRC) && !src->host && ctx->opt_wait_src) {
+                d.wait_ptr = src->received();
+                d.wait_value = (unsigned long long)(x.off + x.size);
+            }
             if (it.mc) {
                 uint8_t *mbase = reinterpret_cast<uint8_t *>(it.mc->va);
                 d.dst = mbase;
                 d.csum = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off() + 256);
                 d.received = reinterpret_cast<unsigned long long *>(mbase + src->trailer_off());
                 d.flags = kFlagMulticast;
+                any_mc = true;
                 for (int dn : it.mc_dsts) {
                     LayerBuf *ml = nullptr;
                     if (find_layer(ctx, dn, x.layer, &ml) == 0) touches(dn, x.layer, ml);
@@ -493,6 +501,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
         part.dev_slot = (int)slot;
         part.round = rounds[ri];
         part.host_src = any_host_src;
+        part.has_mc = any_mc;
         part.n_descs = (int)descs.size();
         part.total_units = units;
         part.bytes = bytes;
@@ -630,7 +639,8 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
                 auto li = ctx->layers[nl.first].find(nl.second);
                 if (li != ctx->layers[nl.first].end()) li->second.writers |= 1ull << (p.dev_slot & 63);
             }
-            LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, p.host_src ? 0 : (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
+            const bool reg_path = p.host_src || (p.has_mc && ctx->opt_mcast_variant == 0);
+            LaunchCfg cfg{ds.n_sm, (int)ctx->opt_ctas_per_sm, reg_path ? 0 : (int)ctx->opt_variant, (int)ctx->opt_reg_cfg, (int)ctx->opt_tma_cfg};
             CUDA_TRY(launch_copy_csum(p.d_descs, p.n_descs, p.total_units, s.unit_shift, ds.counters, cfg, ds.stream, nullptr));
             CUDA_TRY(cudaEventRecord(tp.end, ds.stream));
             if (ds.last_end) CUDA_TRY(cudaEventRecord(ds.last_end, ds.stream));
@@ -1913,6 +1923,8 @@ int dissem_set_option(dissem_ctx *ctx, const char *key, int64_t value) {
     else if (k == "tma_cfg") { if (value < 0 || value > 8) return set_error(DISSEM_EINVAL, "tma_cfg must be 0..8"); ctx->opt_tma_cfg = value; }
     else if (k == "alloc_vmm") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "alloc_vmm must be 0, 1 or 2"); ctx->opt_alloc_vmm = value; }
     else if (k == "mcast") { if (value < 0 || value > 3) return set_error(DISSEM_EINVAL, "mcast must be 0..3"); ctx->opt_mcast = value; }
+    else if (k == "wait_src") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "wait_src must be 0 or 1"); ctx->opt_wait_src = value; }
+    else if (k == "mcast_variant") { if (value < 0 || value > 1) return set_error(DISSEM_EINVAL, "mcast_variant must be 0 or 1"); ctx->opt_mcast_variant = value; }
     else if (k == "pull") { if (value < 0 || value > 2) return set_error(DISSEM_EINVAL, "pull must be 0, 1 or 2"); ctx->opt_pull = value; }
     else if (k == "file_threads") { if (value < 1 || value > 64) return set_error(DISSEM_EINVAL, "file_threads must be 1..64"); ctx->opt_file_threads = value; }
     else if (k == "reg_cfg") { if (value < 0 || value > 9) return set_error(DISSEM_EINVAL, "reg_cfg must be 0..9"); ctx->opt_reg_cfg = value; }
@@ -1934,6 +1946,20 @@ int dissem_get_option(dissem_ctx *ctx, const char *key, int64_t *value_out) {
     else if (k == "tma_cfg") *value_out = ctx->opt_tma_cfg;
     else if (k == "alloc_vmm") *value_out = ctx->opt_alloc_vmm;
     else if (k == "mcast") *value_out = ctx->opt_mcast;
+    else if (k == "mcast_variant") *value_out = ctx->opt_mcast_variant;
+    else if (k == "wait_src") *value_out = ctx->opt_wait_src;
+    else if (k == "wait_timeouts") {
+        // units that gave up waiting for a relay source, over all local GPUs (waits for their streams)
+        int64_t total = 0;
+        for (auto &ds : ctx->devs) {
+            SchedCounters c;
+            CUDA_TRY(cudaSetDevice(ds.dev));
+            CUDA_TRY(cudaStreamSynchronize(ds.stream));
+            CUDA_TRY(cudaMemcpy(&c, ds.counters, sizeof c, cudaMemcpyDeviceToHost));
+            total += c.wait_timeouts;
+        }
+        *value_out = total;
+    }
     else if (k == "mcast_groups") *value_out = ctx->mcast_groups_compiled;     // read-only: multicast descriptors compiled so far
     else if (k == "mcast_supported") {
         std::vector<int> devs;

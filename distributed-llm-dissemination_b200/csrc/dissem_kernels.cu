@@ -121,6 +121,11 @@ copy_csum_kernel(const XferDesc *__restrict__ descs, int n_descs, long long tota
         const uint8_t *__restrict__ src = D->src;
         uint8_t *__restrict__ dst = D->dst;
         const bool mc = (__ldg(&D->flags) & kFlagMulticast) != 0;
+        const unsigned long long *wait_ptr = D->wait_ptr;            // relay hop: the source is still arriving
+        if (wait_ptr) {                                               // uniform per CTA
+            if (tid == 0) wait_for_source(wait_ptr, D->wait_value, counters);
+            __syncthreads();
+        }
 
         const long long base_word = b0 >> 2;                    // word holding the unit's first byte
         long long a0 = (b0 + 15) & ~15ll, a1 = b1 & ~15ll;      // 16-byte aligned body [a0, a1)

@@ -35,15 +35,20 @@ struct __align__(16) XferDesc {
     int flags;
     int prev_units;                  // unit count of the previous (shorter) descriptor in the table, 0 for the first
     int pad[2];
+    // Relay across processes (DISSEM_XFER_WAIT_SRC): the source copy is itself being received during this dissemination.
+    // Before a unit of this transfer is read, the kernel waits until *wait_ptr (the SOURCE copy's received-bytes
+    // counter, which its upstream sender releases after every unit) has reached wait_value = off + size.  NULL = no wait.
+    const unsigned long long *wait_ptr;
+    unsigned long long wait_value;
 };
-static_assert(sizeof(XferDesc) == 80, "XferDesc layout");
+static_assert(sizeof(XferDesc) == 96, "XferDesc layout");
 
 // Scratch the copy kernels need beyond their inputs and outputs: the work-unit ticket and the count of
 // CTAs that have drained (the last one re-arms both for the next launch).
 struct SchedCounters {
     unsigned long long ticket;
     unsigned int done_ctas;
-    unsigned int pad;
+    unsigned int wait_timeouts;      // units that gave up waiting for their source (never re-armed: read by the host)
 };
 
 struct LaunchCfg {
@@ -85,6 +90,26 @@ cudaError_t launch_fill_pattern(uint8_t *dst, long long size, unsigned long long
                                 unsigned long long seed, int n_sm, cudaStream_t stream);
 
 #ifdef __CUDACC__
+// Wait (one thread) until the source copy has received the bytes this transfer is about to forward.  The sender releases
+// the counter at system scope after its data (fence + atomic), so an acquire load here orders the reads that follow;
+// the proxy fence extends that to bulk (TMA) loads.  The wait is bounded (~4 s of SM clocks): a sender that never comes
+// must not hang the GPU; the unit then proceeds, the launch is marked in SchedCounters::wait_timeouts and the delivered
+// bytes will fail verification.
+__device__ __forceinline__ void wait_for_source(const unsigned long long *p, unsigned long long want, SchedCounters *counters) {
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned long long got;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(got) : "l"(p) : "memory");
+        if (got >= want) break;
+        if (clock64() - t0 > 8000000000ll) {
+            atomicAdd(&counters->wait_timeouts, 1u);
+            break;
+        }
+        __nanosleep(256);
+    }
+    asm volatile("fence.proxy.async;" ::: "memory");
+}
+
 // ticket -> (descriptor, slice index within it).  Largest j with L_j <= t; within level j the (m - j) longest
 // descriptors take turns.
 __device__ __forceinline__ int locate_unit(const XferDesc *__restrict__ descs, int n, long long t, long long *slice_idx) {

@@ -147,6 +147,9 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
                     a1 = b1 & ~15ll;
                     if (a0 > b1) a0 = b1;
                     if (a1 < a0) a1 = a0;
+                    // relay hop: the source copy is still arriving; every read of this unit (the bulk loads below, the
+                    // storer's head/tail bytes) happens after this point
+                    if (D->wait_ptr) wait_for_source(D->wait_ptr, D->wait_value, counters);
                 }
                 long long pos = a0;
                 do {

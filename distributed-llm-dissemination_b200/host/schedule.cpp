@@ -121,6 +121,10 @@ int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **ou
     std::vector<dissem_xfer> res;
     std::vector<char> used((size_t)std::max(n, 1), 0);
     auto emit = [&](int src, int dst, const dissem_xfer &x, int hop) {
+        // hops >= 1 read a copy that is still arriving: DISSEM_XFER_WAIT_SRC lets the executing kernel order itself behind the
+        // upstream hop on the device (needed across processes; harmless where round events already order the hops)
+        // (the counter threshold is off + size, which presumes a copy filled from offset 0: whole-layer chains only)
+        const int wait = (hop > 0 && x.off == 0) ? DISSEM_XFER_WAIT_SRC : 0;
         // pieces are cut at multiples of the checksum chunk in LAYER space, so every piece owns whole chunks
         int64_t piece = (x.size + pieces - 1) / pieces;
         piece = (piece + DISSEM_CHUNK_BYTES - 1) / DISSEM_CHUNK_BYTES * DISSEM_CHUNK_BYTES;
@@ -135,7 +139,7 @@ int dissem_plan_relay(const dissem_xfer *in, int n, int pieces, dissem_xfer **ou
             y.dst_node = dst;
             y.off = pos;
             y.size = stop - pos;
-            y.flags = (x.flags & ~(0xFFFF << DISSEM_XFER_ROUND_SHIFT) & ~DISSEM_XFER_PULL) | DISSEM_XFER_ROUND(p + hop);
+            y.flags = (x.flags & ~(0xFFFF << DISSEM_XFER_ROUND_SHIFT) & ~DISSEM_XFER_PULL & ~DISSEM_XFER_WAIT_SRC) | DISSEM_XFER_ROUND(p + hop) | wait;
             res.push_back(y);
             pos = stop;
         }

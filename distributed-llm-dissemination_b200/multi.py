@@ -111,6 +111,52 @@ class RoundedSchedule:
         self.scheds = []
 
 
+XFER_WAIT_SRC = 4
+
+
+def flag_relay_ok(xfers: Sequence) -> bool:
+    """Can the rounds of this plan order themselves on the device across processes?  Yes when every transfer that reads
+    a copy delivered in an EARLIER round of the plan carries DISSEM_XFER_WAIT_SRC (what dissem_plan_relay emits for
+    whole-layer chains)."""
+    first_arrival: Dict[Tuple[int, int], int] = {}
+    for x in xfers:
+        r = (getattr(x, "flags", 0) >> 8) & 0xFFFF
+        key = (x.dst_node, x.layer)
+        first_arrival[key] = min(first_arrival.get(key, r), r)
+    for x in xfers:
+        r = (getattr(x, "flags", 0) >> 8) & 0xFFFF
+        key = (x.src_node, x.layer)
+        if key in first_arrival and first_arrival[key] < r and not (x.flags & XFER_WAIT_SRC):
+            return False
+        if key in first_arrival and first_arrival[key] >= r and r > 0 and key != (x.dst_node, x.layer):
+            return False                    # reads a copy that arrives in the same or a later round: not a relay chain
+    return True
+
+
+class FlagRelaySchedule:
+    """A plan with rounds in the one-process-per-GPU model WITHOUT a host barrier between rounds: every rank compiles all
+    of its rounds into one schedule and launches them back to back; a hop that forwards a piece waits on the device for
+    the source copy's received counter (DISSEM_XFER_WAIT_SRC).  The counters must start at zero: run() resets this rank's
+    destination copies and meets the other ranks ONCE, before the dissemination starts."""
+
+    def __init__(self, eng, xfers: Sequence, owner: Callable[[int], int], rank: int):
+        self.eng = eng
+        eng.set_option("wait_src", 1)
+        self.sched = eng.compile(xfers)
+        self.my_dsts = sorted({(x.dst_node, x.layer) for x in xfers if owner(x.dst_node) == rank})
+        self.scheds = [self.sched]
+
+    def run(self, barrier: Callable[[], None]):
+        for (n, l) in self.my_dsts:
+            self.eng.reset(n, l)
+        barrier()
+        return self.eng.wait_detail(self.eng.launch(self.sched))
+
+    def free(self):
+        self.eng.sched_free(self.sched)
+        self.scheds = []
+
+
 class FdExchange:
     """Passes file descriptors (shareable VMM / multicast handles) between the ranks of one box over unix sockets
     (SCM_RIGHTS).  Plumbing only.  Every descriptor travels with a text key; recv(key) blocks until it has arrived."""

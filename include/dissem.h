@@ -61,10 +61,20 @@ typedef int64_t dissem_sched;    /* one compiled schedule */
 /* FILE: the source is src_node's DISK copy of the layer (dissem_layer_attach_file; LayerSrc with Location = DiskLayer,
  * transport.go:351-367), not its HBM copy.  Such transfers are streamed by dissem_schedule_submit / dissem_send_file. */
 #define DISSEM_XFER_FILE 2
+/* WAIT_SRC: the source copy of this transfer is itself a destination of an earlier round of the same dissemination (a
+ * relay hop).  The kernel that executes the transfer waits, unit by unit, until the source copy's received-bytes
+ * counter has reached off + size before it reads — the counter its upstream sender releases after every unit — so
+ * the hops of a relay chain order themselves ON THE DEVICE even when they run in different processes, with no host
+ * barrier between rounds.  Preconditions (the caller's): the source copy is filled in ascending offset order by ONE
+ * upstream sender whose rounds run one after another (what dissem_plan_relay emits), and its counter was zeroed
+ * (dissem_layer_reset, then a barrier between the processes) before the dissemination started.  The wait is bounded
+ * (~4 s); "wait_timeouts" (dissem_get_option) counts units that gave up.  dissem_plan_relay sets the flag on hops >= 1. */
+#define DISSEM_XFER_WAIT_SRC 4
 /* Bits 8..23 of flags: the transfer's ROUND.  Within one dissem_schedule_* call the transfers of round r start
  * only after every transfer of round r-1 has completed on every GPU of this process (device-side event waits, no
  * host round trip).  A relay plan (dissem_plan_relay) forwards in round r the piece that arrived in round r-1.
- * Across processes rounds are not synchronised: submit one round per call and separate them yourself. */
+ * Across processes rounds are not synchronised by the engine: either the transfers carry DISSEM_XFER_WAIT_SRC (device-side
+ * waits on the received counters; submit all rounds in one call), or submit one round per call and separate them yourself. */
 #define DISSEM_XFER_ROUND_SHIFT 8
 #define DISSEM_XFER_ROUND(r) (((r) & 0xFFFF) << DISSEM_XFER_ROUND_SHIFT)
 
@@ -294,13 +304,19 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
 /* key: "ctas_per_sm" (0 = occupancy-derived), "variant" (0 = register path, 1 = TMA bulk-staged path),
  * "reg_cfg" (register-path shape, threads x 16-byte loads in flight: 0 256x4, 1 512x4 (default), 2 256x8,
  * 3 512x8, 4 1024x4, 5 1024x2, 6 512x2; 7/8/9 = 512x2, 512x4, 256x4 with 32-byte loads and stores),
- * "tma_cfg" (TMA ring shape, stage bytes x stages: 0 16Kx6 (default), 1 32Kx3, 2 8Kx12, 3 16Kx4, 4 8Kx6, 5 4Kx12),
+ * "tma_cfg" (TMA ring shape, stage bytes x stages: 0 16Kx6 (default), 1 32Kx3, 2 8Kx12, 3 16Kx4, 4 8Kx6, 5 4Kx12;
+ *  6 / 7 = 16Kx6 with 8 / 14 checksum warps, 8 = 8Kx6 with 14: probe shapes for multicast units),
  * "alloc_vmm" (1 = dissem_layer_alloc uses the VMM API so that layers can be bound to NVLS multicast objects;
  *  2 = the same, shareable with other processes through dissem_layer_export_fd),
  * "mcast" (transfers of the same bytes from one source to several GPUs can go as ONE NVLS multicast store stream
  *  when every buffer involved is VMM-backed and local.  1 (default) = do so when a cost model built on the measured
  *  port rates says the plan gets shorter (i.e. it is bound by a source's egress); 3 = always; 0 = never (unicast
  *  fan-out); 2 = always, and single-destination transfers to another GPU too (a testing aid)),
+ * "wait_src" (0 (default) = DISSEM_XFER_WAIT_SRC flags are ignored: inside one process round events already order relay
+ *  hops, and a relaunch without dissem_layer_reset would find the counters already past their thresholds; 1 = honour
+ *  them: the mode for one process per GPU, see DISSEM_XFER_WAIT_SRC), read-only "wait_timeouts",
+ * "mcast_variant" (kernel for schedule parts that carry multicast units: 0 (default) = register path whatever "variant"
+ *  says, 1 = follow "variant"; transfers whose offset or size is not a multiple of 16 bytes are never multicast),
  * read-only: "mcast_supported" (do all local GPUs support multicast objects), "mcast_groups" (multicast
  *  descriptors compiled so far),
  * "unit_bytes" (0 = auto; else power of two in [4096, 262144]),

@@ -865,10 +865,10 @@ def test_push_waits_for_the_destination_gpus_own_stream():
     if _n_gpus() < 2:
         pytest.skip("needs 2 GPUs")
     big, size = 512 << 20, 9 * d.CHUNK_BYTES + 4321
-    want = o.fill_bytes(o.FILL_PATTERN, 7, size, SEED)
     with d.Engine([0, 1, 1]) as eng:
-        eng.alloc(0, 7, size)
-        eng.fill(0, 7, d.FILL_PATTERN, SEED)
+        for rep in range(8):                          # a transfer names ONE layer id: the source holds layers 100..107
+            eng.alloc(0, 100 + rep, size)
+            eng.fill(0, 100 + rep, d.FILL_PATTERN, SEED)
         for l in (50, 51):
             eng.alloc(1, l, big)
             eng.fill(1, l, d.FILL_PATTERN, SEED)
@@ -883,6 +883,7 @@ def test_push_waits_for_the_destination_gpus_own_stream():
             eng.wait(t)
             for b in tickets:
                 eng.wait(b)
+            want = o.fill_bytes(o.FILL_PATTERN, 100 + rep, size, SEED)
             assert eng.received(1, 100 + rep) == size, rep
             assert np.array_equal(eng.checksums(1, 100 + rep), o.checksum(want)), rep
             assert np.array_equal(eng.read(1, 100 + rep), want), rep

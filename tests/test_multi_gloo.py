@@ -121,3 +121,23 @@ def test_fd_exchange_passes_descriptors_between_processes(tmp_path):
             fx.recv("never", timeout=0.2)
     finally:
         fx.close()
+
+
+def test_flag_relay_ok_recognises_device_ordered_relay_plans():
+    """multi.flag_relay_ok: dissem_plan_relay's whole-layer chains carry DISSEM_XFER_WAIT_SRC on every hop that reads a
+    copy delivered in an earlier round, so their rounds can order themselves on the device across processes; a plan
+    that forwards without the flag (or forwards a fragment chain, which gets none) needs the barrier per round."""
+    size = 8 * d.CHUNK_BYTES
+    base = [d.Xfer(0, dst, 5, 0, 0, size, size) for dst in (1, 2, 3)] + [d.Xfer(3, 1, 6, 0, 0, size, size)]
+    relay = d.plan_relay(base, 4)
+    hops = [x for x in relay if x.layer == 5 and x.src_node != 0]
+    assert hops and all(x.flags & multi.XFER_WAIT_SRC for x in hops)
+    assert not any(x.flags & multi.XFER_WAIT_SRC for x in relay if x.src_node == 0 or x.layer == 6)
+    assert multi.flag_relay_ok(relay)
+    assert multi.flag_relay_ok(d.plan_directions(relay, [0, 1, 2, 3]))          # direction choice keeps the flag
+    assert all((a.flags & 4) == (b.flags & 4) for a, b in zip(relay, d.plan_directions(relay, [0, 1, 2, 3])))
+    stripped = [d.Xfer(x.src_node, x.dst_node, x.layer, x.flags & ~multi.XFER_WAIT_SRC, x.off, x.size, x.total) for x in relay]
+    assert not multi.flag_relay_ok(stripped)
+    frag = d.plan_relay([d.Xfer(0, dst, 5, 0, d.CHUNK_BYTES, size - d.CHUNK_BYTES, size) for dst in (1, 2)], 2)
+    assert not any(x.flags & multi.XFER_WAIT_SRC for x in frag) and not multi.flag_relay_ok(frag)
+    assert multi.flag_relay_ok(base)                                            # no rounds at all: nothing to order

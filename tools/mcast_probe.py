@@ -21,6 +21,7 @@ def run(n, layers, size, dsts, mcast, variant, reg_cfg, tma_cfg, ctas, reps, pul
         eng.set_option("alloc_vmm", 1)
         eng.set_option("mcast", mcast)
         eng.set_option("variant", variant)
+        eng.set_option("mcast_variant", 1)          # the sweep chooses the kernel itself
         eng.set_option("reg_cfg", reg_cfg)
         eng.set_option("tma_cfg", tma_cfg)
         eng.set_option("ctas_per_sm", ctas)
@@ -54,6 +55,7 @@ def main():
     ap.add_argument("--dsts", default="")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--one", action="store_true", help="one multicast case only (register 512x4, all other GPUs as destinations): the ncu target")
     args = ap.parse_args()
     n = min(torch.cuda.device_count(), 8)
     if n < 2:
@@ -61,6 +63,10 @@ def main():
         return
     ks = [int(v) for v in args.dsts.split(",") if v] or sorted({1, n - 1})
     L, S, R = args.layers, args.size, args.reps
+    if args.one:
+        k = n - 1
+        run(n, L, S, list(range(1, k + 1)), 2 if k == 1 else 3, 0, 1, 0, 0, 1, tag=f"multicast x{k}, register cfg 1")
+        return
     # unicast references: one destination
     run(n, L, S, [1], 0, 1, 1, 0, 0, R, tag="unicast push, TMA")
     run(n, L, S, [1], 0, 0, 1, 0, 0, R, tag="unicast push, register 512x4")
