@@ -886,10 +886,10 @@ def run_ours(args, rank, world, local_rank):
                     eng.write(node, layer, None, off=a, ptr=p.value + (a - lo), size=b - a)
 
         def e2e_step():
-            upload()
+            upload()                           # asynchronous: the planning below runs while the copy engine works
+            _p, pl, _pc = make_plan()
             if dist is not None:               # a peer process's kernel cannot wait for this process's upload: meet first
                 barrier()
-            _p, pl, _pc = make_plan()
             if dist is not None and any(d.xfer_round(x) for x in pl):      # rounds are not ordered across processes
                 r_ = Runner(eng, multi, pl, barrier, True, owner=owner, rank=rank)
                 r_.step()

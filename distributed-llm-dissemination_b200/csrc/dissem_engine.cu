@@ -284,6 +284,10 @@ static McObject *get_or_make_mcast(dissem_ctx *ctx, int layer, int src_node, con
     return ins.first->second.valid() ? &ins.first->second : nullptr;
 }
 
+// port rates behind the multicast cost model, GB/s (tools/mcast_probe.py on 2 and 4 B200s, profiles/r02_n*_mcast_probe.jsonl)
+constexpr double kUnicastPushGBps = 713.0;
+constexpr double kMulticastGBps = 560.0;
+
 struct CompileItem {
     dissem_xfer x;
     McObject *mc = nullptr;      // set: one multicast stream standing for n_dsts transfers of the same bytes
@@ -342,9 +346,10 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             for (int m : g.members) grouped[m] = 1;
             groups.push_back(std::move(g));
         }
-        // Cost model (opt_mcast == 1).  Measured on B200 / NVLink 5 (profiles/r01_summary.md): a unicast push stream
-        // moves ~710 GB/s per port; an NVLS multicast stream leaves its source at ~634 GB/s but lands at only
-        // ~537 GB/s per destination port.  Multicast therefore pays only when the plan is bound by a source's egress:
+        // Cost model (opt_mcast == 1).  Measured on B200 / NVLink 5 with tools/mcast_probe.py (profiles/r02_n2_mcast_probe.jsonl,
+        // r02_n4_mcast_probe.jsonl): a unicast push stream moves ~713 GB/s out of a port; an NVLS multicast stream leaves
+        // its source at ~560 GB/s whatever the kernel shape and the number of destinations (1, 2 or 3), and each member
+        // receives at that same rate.  Multicast therefore pays only when the plan is bound by a source's egress:
         // compare max-port time with every group sent as unicast copies against every group sent once.
         bool use_mc = !groups.empty();
         if (ctx->opt_mcast == 1 && use_mc) {
@@ -360,8 +365,8 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             }
             for (auto &g : groups) eg_mc[gpu_of(xfers[g.members[0]].src_node)] += (double)xfers[g.members[0]].size;
             auto mx = [](const std::map<int, double> &m) { double v = 0; for (auto &kv : m) v = std::max(v, kv.second); return v; };
-            const double t_uni = std::max(mx(eg_uni), mx(ing)) / 710.0;
-            const double t_mc = std::max(mx(eg_mc) / 634.0, mx(ing) / 537.0);
+            const double t_uni = std::max(mx(eg_uni), mx(ing)) / kUnicastPushGBps;
+            const double t_mc = std::max(mx(eg_mc), mx(ing)) / kMulticastGBps;
             use_mc = t_mc < t_uni;
             if (!use_mc) ctx->mcast_note = "cost model: the plan is not egress-bound, unicast copies are faster than multicast";
         }

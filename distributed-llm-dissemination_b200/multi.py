@@ -6,6 +6,8 @@ Sharding follows SURVEY §8(e): the units are independent (dest, layer) transfer
 owns the SOURCE node (push model); there is no data-path collective."""
 from __future__ import annotations
 
+import os
+
 from typing import Callable, Dict, Iterable, List, Sequence, Tuple
 
 
@@ -290,7 +292,11 @@ class SharedStore:
                     self.sent.add((n, l, r))
             for (n, l, total, r) in touches:
                 if r == self.rank and (n, l) not in self.imported:
-                    self.eng.import_fd(n, l, total, self.fx.recv(f"buf:{n}:{l}:{r}"))
+                    fd = self.fx.recv(f"buf:{n}:{l}:{r}")
+                    try:
+                        self.eng.import_fd(n, l, total, fd)
+                    finally:
+                        os.close(fd)                 # the mapping keeps the allocation alive; the descriptor is done
                     self.imported.add((n, l))
         self.dist.barrier()
 
@@ -340,7 +346,11 @@ def setup_mcast(eng, fx, dist, groups: Sequence[Tuple[int, int, List[int]]], own
         for (layer, src, dsts) in groups:
             for dn in dsts:
                 if owner(dn) == rank:
-                    eng.mcast_join(layer, src, dsts, dn, fx.recv(f"mc:{layer}:{src}:{dn}"))
+                    fd = fx.recv(f"mc:{layer}:{src}:{dn}")
+                    try:
+                        eng.mcast_join(layer, src, dsts, dn, fd)
+                    finally:
+                        os.close(fd)
     except Exception as e:                                  # noqa: BLE001
         ok, why = False, f"join: {e}"
     if not agreed(ok):
