@@ -113,6 +113,7 @@ struct SchedPart {
     int pool_slot = -1;               // >= 0: d_descs points into the device's descriptor pool
     int round = 0;
     bool host_src = false;            // reads pinned host memory: runs the register kernel
+    bool needs_zero = true;           // false: every descriptor stores whole-chunk sums and owns no partial chunk -> no zeroing kernel
     bool has_mc = false;              // carries NVLS multicast units: runs the register kernel (multimem.st straight from the
                                       // loaded registers: 570 GB/s against 533 GB/s through the shared-memory ring, any ring
                                       // shape: profiles/r02_n2_mcast_probe.jsonl)
@@ -481,6 +482,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
                 touches(x.dst_node, x.layer, dst);
                 written(x.dst_node, x.layer);
             }
+            if (out->unit_shift == kChunkShift) d.flags |= kFlagStoreSums;       // units are whole chunks: sums stored, not added
             units += units_of(x.off, x.size, out->unit_shift);
             bytes += x.size * (int64_t)it.n_dsts;
             descs.push_back(d);
@@ -564,6 +566,12 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             }
     }
     for (size_t pi = 0; pi < out->parts.size(); ++pi) {
+        bool zero = false;
+        for (auto &d : part_descs[pi])
+            if (d.csum && (!(d.flags & kFlagStoreSums) || (d.flags & (kFlagZeroHead | kFlagZeroTail)))) zero = true;
+        out->parts[pi].needs_zero = zero;
+    }
+    for (size_t pi = 0; pi < out->parts.size(); ++pi) {
         SchedPart &part = out->parts[pi];
         DeviceState &pds = ctx->devs[part.dev_slot];
         CUDA_TRY(cudaSetDevice(pds.dev));
@@ -629,7 +637,7 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
             CUDA_TRY(take_event(ctx, ds.dev, &ntp.end));
             tp = ntp;
             CUDA_TRY(cudaEventRecord(tp.start, ds.stream));
-            CUDA_TRY(launch_zero_csum(p.d_descs, p.n_descs, ds.stream));
+            if (p.needs_zero) CUDA_TRY(launch_zero_csum(p.d_descs, p.n_descs, ds.stream));
             CUDA_TRY(cudaEventRecord(tp.mid, ds.stream));
         }
         std::vector<cudaEvent_t> this_round;
@@ -638,8 +646,8 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
             DeviceState &ds = ctx->devs[p.dev_slot];
             TicketPart &tp = t->parts[first_tp + (k - i)];
             CUDA_TRY(cudaSetDevice(ds.dev));
-            for (size_t m = i; m < j; ++m)
-                if (m != k) CUDA_TRY(cudaStreamWaitEvent(ds.stream, t->parts[first_tp + (m - i)].mid, 0));
+            for (size_t m = i; m < j; ++m)      // (a part that zeroes nothing has nothing the others must wait for)
+                if (m != k && s.parts[m].needs_zero) CUDA_TRY(cudaStreamWaitEvent(ds.stream, t->parts[first_tp + (m - i)].mid, 0));
             for (auto &nl : p.writes) {
                 auto li = ctx->layers[nl.first].find(nl.second);
                 if (li != ctx->layers[nl.first].end()) li->second.writers |= 1ull << (p.dev_slot & 63);
@@ -1492,7 +1500,11 @@ int dissem_schedule_info(dissem_ctx *ctx, dissem_sched sched, int64_t *units_out
     auto it = ctx->scheds.find(sched);
     if (it == ctx->scheds.end()) return set_error(DISSEM_ENOENT, "unknown schedule %lld", (long long)sched);
     if (units_out) *units_out = it->second.units;
-    if (launches_out) *launches_out = 2 * (int)it->second.parts.size();   // zero_csum + copy_csum per source GPU
+    if (launches_out) {                                                     // copy_csum (+ zero_csum where a part needs it) per executing GPU and round
+        int n_launch = 0;
+        for (auto &p : it->second.parts) n_launch += p.needs_zero ? 2 : 1;
+        *launches_out = n_launch;
+    }
     if (bytes_out) *bytes_out = it->second.bytes;
     return DISSEM_OK;
 }

@@ -225,7 +225,15 @@ copy_csum_kernel(const XferDesc *__restrict__ descs, int n_descs, long long tota
                 unsigned long long *cs = D->csum;
                 if (cs) {
                     const long long c = b0 >> kChunkShift;
-                    if (mc) { red_multicast_u64(cs + 2 * c, A); red_multicast_u64(cs + 2 * c + 1, B); }
+                    long long ce = (c + 1) << kChunkShift;
+                    const long long total = __ldg(&D->total);
+                    if (ce > total) ce = total;
+                    // the unit is its chunk (kFlagStoreSums): the one and only contribution -> plain stores, no prior zeroing
+                    const bool whole = (__ldg(&D->flags) & kFlagStoreSums) && b0 == (c << kChunkShift) && b1 == ce;
+                    if (whole) {
+                        if (mc) { st_multicast_u64(cs + 2 * c, A); st_multicast_u64(cs + 2 * c + 1, B); }
+                        else { cs[2 * c] = A; cs[2 * c + 1] = B; }
+                    } else if (mc) { red_multicast_u64(cs + 2 * c, A); red_multicast_u64(cs + 2 * c + 1, B); }
                     else { atomicAdd(cs + 2 * c, A); atomicAdd(cs + 2 * c + 1, B); }
                 }
                 unsigned long long *rcv = D->received;
@@ -262,8 +270,9 @@ __global__ void zero_csum_kernel(const XferDesc *__restrict__ descs, int n_descs
         if (!cs) continue;
         const long long off = D->off, end = D->off + D->size, total = D->total;
         const bool mc = (D->flags & kFlagMulticast) != 0;
+        const bool stored = (D->flags & kFlagStoreSums) != 0;                   // whole chunks are stored, not accumulated
         const long long c0 = (off + kChunkBytes - 1) >> kChunkShift;            // first chunk starting inside
-        for (long long c = c0 + lane; (c << kChunkShift) < end; c += 32) {
+        for (long long c = c0 + lane; !stored && (c << kChunkShift) < end; c += 32) {
             long long ce = (c + 1) << kChunkShift;
             if (ce > total) ce = total;
             if (ce <= end) {

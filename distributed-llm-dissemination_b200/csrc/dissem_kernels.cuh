@@ -13,6 +13,10 @@ enum : int {
     kFlagMulticast = 1,   // dst / csum / received are NVLS multicast addresses (multimem.* only)
     kFlagZeroHead = 2,    // this descriptor owns the zeroing of the partially covered chunk its fragment starts in
     kFlagZeroTail = 4,    // ... and of the partially covered chunk it ends in
+    // Work units are whole checksum chunks (unit size == chunk size): a unit that covers its chunk completely is the ONLY
+    // contribution to that table entry, so its sums are stored, not added, and the entry needs no zeroing beforehand
+    // (set by the schedule compiler; partially covered chunks at a fragment's ends still accumulate with atomics).
+    kFlagStoreSums = 8,
 };
 
 // One transfer as the kernels see it: bytes [off, off+size) of a layer, from the source copy to the

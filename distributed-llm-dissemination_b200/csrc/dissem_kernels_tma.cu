@@ -31,7 +31,7 @@ struct StageMeta {
     long long b0, b1;     // the unit's byte range in layer space
     int n;                // bytes staged (multiple of 16, may be 0)
     int flags;            // kMetaLast: last stage of its unit; kMetaEnd: no more work
-    int mc;
+    int mc;               // bit 0: multicast unit; bit 1: whole-chunk unit whose sums are stored (kFlagStoreSums)
     int pad;
 };
 
@@ -94,6 +94,9 @@ __device__ __forceinline__ void st_multicast16(void *p, const uint4 &v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(__uint_as_float(v.x)),
                  "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
                  : "memory");
+}
+__device__ __forceinline__ void st_multicast64(unsigned long long *p, unsigned long long v) {
+    asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void red_multicast64(unsigned long long *p, unsigned long long v) {
     asm volatile("multimem.red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -172,7 +175,13 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
                         m.b0 = b0;
                         m.b1 = b1;
                         m.n = (int)n;
-                        m.mc = (D->flags & kFlagMulticast) ? 1 : 0;
+                        {
+                            // bit 0: multicast unit; bit 1: the unit covers its whole chunk and the sums may be stored
+                            long long ce = ((b0 >> kChunkShift) + 1) << kChunkShift;
+                            if (ce > D->total) ce = D->total;
+                            const bool whole = (D->flags & kFlagStoreSums) && (b0 & (kChunkBytes - 1)) == 0 && b1 == ce;
+                            m.mc = ((D->flags & kFlagMulticast) ? 1 : 0) | (whole ? 2 : 0);
+                        }
                         m.flags = (pos + n >= a1) ? kMetaLast : 0;
                         if (n > 0) {
                             mbar_arrive_expect_tx(&sm.full[s], (unsigned)n);
@@ -225,12 +234,15 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
                     const unsigned long long B = (unsigned long long)(base_word + 1) * A + S2;
                     if (m.csum) {
                         const long long c = m.b0 >> kChunkShift;
-                        if (m.mc) { red_multicast64(m.csum + 2 * c, A); red_multicast64(m.csum + 2 * c + 1, B); }
+                        if (m.mc & 2) {              // the unit is its chunk (kFlagStoreSums): stored, no prior zeroing needed
+                            if (m.mc & 1) { st_multicast64(m.csum + 2 * c, A); st_multicast64(m.csum + 2 * c + 1, B); }
+                            else { m.csum[2 * c] = A; m.csum[2 * c + 1] = B; }
+                        } else if (m.mc & 1) { red_multicast64(m.csum + 2 * c, A); red_multicast64(m.csum + 2 * c + 1, B); }
                         else { atomicAdd(m.csum + 2 * c, A); atomicAdd(m.csum + 2 * c + 1, B); }
                     }
                     if (m.received) {
                         __threadfence_system();
-                        if (m.mc) red_multicast64(m.received, (unsigned long long)(m.b1 - m.b0));
+                        if (m.mc & 1) red_multicast64(m.received, (unsigned long long)(m.b1 - m.b0));
                         else atomicAdd_system(m.received, (unsigned long long)(m.b1 - m.b0));
                     }
                 } else {
@@ -248,7 +260,7 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
                 } else {
                     const int n = sm.meta[s].n;
                     uint8_t *dst = sm.meta[s].dst;
-                    if (dst && !sm.meta[s].mc && n > 0) {
+                    if (dst && !(sm.meta[s].mc & 1) && n > 0) {
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         tma_store(dst + sm.meta[s].pos, sm.data[s], (unsigned)n);
                     }
@@ -278,7 +290,7 @@ copy_csum_tma_kernel(const XferDesc *__restrict__ descs, int n_descs, long long 
             const unsigned int k_stage = (unsigned int)((pos >> 2) - base_word);
             const uint4 *tile = reinterpret_cast<const uint4 *>(sm.data[s]);
             const int nvec = n >> 4;
-            const bool mc = sm.meta[s].mc != 0 && sm.meta[s].dst != nullptr;
+            const bool mc = (sm.meta[s].mc & 1) != 0 && sm.meta[s].dst != nullptr;
             uint4 *mcdst = mc ? reinterpret_cast<uint4 *>(sm.meta[s].dst + pos) : nullptr;
             int v = ctid;
             if (mc) {
