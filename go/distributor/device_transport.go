@@ -19,6 +19,7 @@ import (
 	"encoding/json"
 	"fmt"
 	"sync"
+	"unsafe"
 )
 
 // DeviceLayer marks a LayerSrc whose bytes live in the engine's HBM store under (node, layer).
@@ -30,18 +31,62 @@ type deviceFabric struct {
 	ctx   *C.dissem_ctx
 	mu    sync.RWMutex
 	peers map[NodeID]*DeviceTransport
+	// The C ABI names nodes by a dense index 0..n-1; the reference's NodeIDs are arbitrary uints (config "Id").
+	index    map[NodeID]C.int
+	uploaded map[[2]uint]bool // (node, layer) whose host InmemData already sits in HBM
+	refs     int              // transports still open; the last Close releases the context
 }
 
-func NewDeviceFabric(deviceOfNode []int) (*deviceFabric, error) {
+// NewDeviceFabric: ids[i] is the NodeID of the config's i-th node, deviceOfNode[i] the CUDA ordinal it lives on.
+func NewDeviceFabric(ids []NodeID, deviceOfNode []int) (*deviceFabric, error) {
+	if len(ids) == 0 || len(ids) != len(deviceOfNode) {
+		return nil, fmt.Errorf("NewDeviceFabric: need one device per node and at least one node (got %d ids, %d devices)", len(ids), len(deviceOfNode))
+	}
 	devs := make([]C.int, len(deviceOfNode))
+	index := make(map[NodeID]C.int, len(ids))
 	for i, d := range deviceOfNode {
 		devs[i] = C.int(d)
+		index[ids[i]] = C.int(i)
 	}
 	var ctx *C.dissem_ctx
 	if rc := C.dissem_init(C.int(len(devs)), &devs[0], &ctx); rc != 0 {
 		return nil, fmt.Errorf("dissem_init: %s", C.GoString(C.dissem_last_error()))
 	}
-	return &deviceFabric{ctx: ctx, peers: make(map[NodeID]*DeviceTransport)}, nil
+	return &deviceFabric{ctx: ctx, peers: make(map[NodeID]*DeviceTransport), index: index, uploaded: make(map[[2]uint]bool)}, nil
+}
+
+func (f *deviceFabric) idx(id NodeID) (C.int, error) {
+	i, ok := f.index[id]
+	if !ok {
+		return 0, fmt.Errorf("node %d is not part of this fabric", id)
+	}
+	return i, nil
+}
+
+// ensureSource: the reference keeps an in-memory layer as a host slice (LayerSrc.InmemData, cmd/config.go:159-171).  The
+// engine sends from HBM, so the first Send of a layer uploads the sender's slice once (dissem_layer_alloc +
+// dissem_layer_write).  A deployment that never wants layers in host memory changes CreateInmemLayer instead to call
+// dissem_layer_alloc / dissem_layer_fill and to leave InmemData empty; then there is nothing to upload here.
+func (f *deviceFabric) ensureSource(node C.int, id NodeID, layer LayerID, src LayerSrc) error {
+	if src.InmemData == nil || len(*src.InmemData) == 0 {
+		return nil
+	}
+	key := [2]uint{uint(id), uint(layer)}
+	f.mu.Lock()
+	defer f.mu.Unlock()
+	if f.uploaded[key] {
+		return nil
+	}
+	if C.dissem_layer_info(f.ctx, node, C.int(layer), nil, nil) != 0 {
+		if rc := C.dissem_layer_alloc(f.ctx, node, C.int(layer), C.int64_t(len(*src.InmemData))); rc != 0 {
+			return derr("dissem_layer_alloc(source)")
+		}
+	}
+	if rc := C.dissem_layer_write(f.ctx, node, C.int(layer), unsafe.Pointer(&(*src.InmemData)[0]), 0, C.int64_t(len(*src.InmemData))); rc != 0 {
+		return derr("dissem_layer_write")
+	}
+	f.uploaded[key] = true
+	return nil
 }
 
 type DeviceTransport struct {
@@ -54,6 +99,7 @@ func NewDeviceTransport(f *deviceFabric, me NodeID, bufSize uint) *DeviceTranspo
 	t := &DeviceTransport{fabric: f, me: me, incomingMsgChan: make(chan Message, bufSize)}
 	f.mu.Lock()
 	f.peers[me] = t
+	f.refs++
 	f.mu.Unlock()
 	return t
 }
@@ -71,9 +117,22 @@ func (t *DeviceTransport) Send(destID NodeID, message Message) error {
 	}
 	if lm, ok := message.(*layerMsg); ok {
 		ctx := t.fabric.ctx
+		src, err := t.fabric.idx(lm.SrcID)
+		if err != nil {
+			return err
+		}
+		dst, err := t.fabric.idx(destID)
+		if err != nil {
+			return err
+		}
+		if lm.LayerSrc.Meta.Location != DiskLayer {
+			if err := t.fabric.ensureSource(src, lm.SrcID, lm.LayerID, lm.LayerSrc); err != nil {
+				return err
+			}
+		}
 		// receiver side of transport.go:201: make sure the destination buffer exists
-		if C.dissem_layer_info(ctx, C.int(destID), C.int(lm.LayerID), nil, nil) != 0 {
-			if rc := C.dissem_layer_alloc(ctx, C.int(destID), C.int(lm.LayerID), C.int64_t(lm.TotalSize)); rc != 0 && rc != C.DISSEM_EEXIST {
+		if C.dissem_layer_info(ctx, dst, C.int(lm.LayerID), nil, nil) != 0 {
+			if rc := C.dissem_layer_alloc(ctx, dst, C.int(lm.LayerID), C.int64_t(lm.TotalSize)); rc != 0 && rc != C.DISSEM_EEXIST {
 				return derr("dissem_layer_alloc")
 			}
 		}
@@ -81,11 +140,11 @@ func (t *DeviceTransport) Send(destID NodeID, message Message) error {
 		if lm.LayerSrc.Meta.Location == DiskLayer {
 			// transport.go:351-367: the layer is a file; it was registered with dissem_layer_attach_file(node, layer,
 			// LayerSrc.Fp, 0, DataSize) when CreateDiskLayer made it, and is streamed through pinned staging buffers
-			if rc := C.dissem_send_file(ctx, C.int(lm.SrcID), C.int(destID), C.int(lm.LayerID),
+			if rc := C.dissem_send_file(ctx, src, dst, C.int(lm.LayerID),
 				C.int64_t(lm.LayerSrc.Offset), C.int64_t(lm.LayerSrc.DataSize), C.int64_t(lm.TotalSize), &ticket); rc != 0 {
 				return derr("dissem_send_file")
 			}
-		} else if rc := C.dissem_send(ctx, C.int(lm.SrcID), C.int(destID), C.int(lm.LayerID),
+		} else if rc := C.dissem_send(ctx, src, dst, C.int(lm.LayerID),
 			C.int64_t(lm.LayerSrc.Offset), C.int64_t(lm.LayerSrc.DataSize), C.int64_t(lm.TotalSize), &ticket); rc != 0 {
 			return derr("dissem_send")
 		}
@@ -127,7 +186,28 @@ func (t *DeviceTransport) Broadcast(m Message) error {
 }
 func (t *DeviceTransport) Deliver() <-chan Message { return t.incomingMsgChan }
 func (t *DeviceTransport) GetAddress() string      { return fmt.Sprintf("gpu:%d", t.me) }
-func (t *DeviceTransport) Close() error            { return nil } // the fabric owns the context: C.dissem_close(f.ctx)
+
+// Close (transport.go:474-491): the transport leaves the fabric; the last one out releases the engine's context and with
+// it every HBM buffer.
+func (t *DeviceTransport) Close() error {
+	f := t.fabric
+	f.mu.Lock()
+	defer f.mu.Unlock()
+	if _, ok := f.peers[t.me]; !ok {
+		return nil
+	}
+	delete(f.peers, t.me)
+	close(t.incomingMsgChan)
+	f.refs--
+	if f.refs == 0 && f.ctx != nil {
+		rc := C.dissem_close(f.ctx)
+		f.ctx = nil
+		if rc != 0 {
+			return derr("dissem_close")
+		}
+	}
+	return nil
+}
 
 // encodeEnvelope / decodeEnvelope: the control plane keeps the reference's wire format, so that what a node receives is
 // what TCP would have delivered (unexported fields such as ackMsg.location are lost, message.go:62-66).
