@@ -48,3 +48,19 @@ def test_our_arm_line():
     assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1
     c = j["clocks"]
     assert not ({"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} & set(c["reasons"]))
+
+
+def test_go_probe_reports_why():
+    """the reference arm probes for a Go toolchain + offline module cache at run time and says what it
+    found.  On this image (and the GPU boxes) there is no `go`: the probe must say so, never raise, never download."""
+    sys.path.insert(0, ROOT)
+    import importlib
+    bench = importlib.import_module("bench")
+    p = bench.probe_go()
+    assert isinstance(p, dict) and "usable" in p
+    if not p["usable"]:
+        assert p["why"]
+    else:
+        assert os.path.exists(p["binary"])
+    j = _run("--impl", "reference", "--steps", "1", "--warmup", "0")
+    assert "Go probe:" in j["note"]
