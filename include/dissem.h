@@ -189,6 +189,13 @@ int dissem_send_file(dissem_ctx *ctx, int src_node, int dst_node, int layer, int
  * GPU.  dissem_schedule_submit = compile + launch + free. */
 int dissem_schedule_submit(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_ticket *out);
 int dissem_schedule_compile(dissem_ctx *ctx, const dissem_xfer *xfers, int n, dissem_sched *out);
+/* A compiled schedule may be launched again and again, also with earlier launches still in flight: the checksum entries
+ * it fills are stored or re-zeroed by the launch itself (partially covered chunks shared by several fragments of the
+ * schedule get one owner; where those fragments run on different GPUs of this process, the launch first waits for the
+ * other GPUs' previous launch).  Two limits: a chunk the schedule covers only in part keeps accumulating (it also takes
+ * bytes from other submissions), and with ONE PROCESS PER GPU a chunk shared by fragments of different processes cannot
+ * be re-zeroed by anybody — run dissem_plan_align on the plan first (dissem_plan_optimize does), or dissem_layer_reset the
+ * destinations between launches.  The received counters are monotonic by design. */
 int dissem_schedule_launch(dissem_ctx *ctx, dissem_sched sched, dissem_ticket *out);
 int dissem_schedule_free(dissem_ctx *ctx, dissem_sched sched);
 /* units_out: work units of the compiled schedule; launches_out: kernel launches one dissem_schedule_launch
