@@ -941,3 +941,52 @@ def test_a_blocked_table_read_does_not_hold_up_other_senders():
         assert accept_s < blocked["s"] / 2, (accept_s, blocked)
         assert np.array_equal(eng.read(3, 9), o.fill_bytes(o.FILL_PATTERN, 9, 4096, SEED))
         eng.sched_free(s)
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_relay_with_device_side_waits_in_one_process(variant):
+    """DISSEM_XFER_WAIT_SRC with "wait_src" on, inside ONE process: round events already order the hops, so every wait finds
+    its counter past the threshold — the kernels' wait path runs (both variants), nothing times out, and the store equals
+    the oracle's.  (Across processes the same flags carry the ordering; bench.py's parity leg checks that on >= 2 GPUs.)"""
+    size = 11 * d.CHUNK_BYTES + 4321
+    n = max(1, min(_n_gpus(), 4))
+    want = o.fill_bytes(o.FILL_PATTERN, 3, size, SEED)
+    with d.Engine([i % n for i in range(4)]) as eng:
+        eng.set_option("variant", variant)
+        eng.set_option("wait_src", 1)
+        eng.alloc(0, 3, size)
+        eng.fill(0, 3, d.FILL_PATTERN, SEED)
+        for node in (1, 2, 3):
+            eng.alloc(node, 3, size)
+            eng.fill(node, 3, d.FILL_POISON)
+        plan = d.plan_directions(d.plan_relay([d.Xfer(0, node, 3, 0, 0, size, size) for node in (1, 2, 3)], 4), [i % n for i in range(4)])
+        assert any(x.flags & 4 for x in plan)
+        eng.wait(eng.submit(plan))
+        assert eng.get_option("wait_timeouts") == 0
+        for node in (1, 2, 3):
+            assert np.array_equal(eng.read(node, 3), want), node
+            assert np.array_equal(eng.checksums(node, 3), o.checksum(want)), node
+            assert eng.received(node, 3) == size
+
+
+def test_a_relay_wait_is_bounded():
+    """A hop whose source never arrives must not hang the GPU: the unit gives up after ~4 s of SM clocks, the launch
+    completes, "wait_timeouts" counts it, and the table shows that what was forwarded is not the layer."""
+    size = d.CHUNK_BYTES                              # one work unit: one bounded wait
+    with d.Engine([0, 0, 0]) as eng:
+        eng.set_option("wait_src", 1)
+        for node in (1, 2):
+            eng.alloc(node, 9, size)
+            eng.fill(node, 9, d.FILL_POISON)
+        import time
+        t0 = time.perf_counter()
+        eng.wait(eng.submit([d.Xfer(1, 2, 9, 4, 0, size, size)]))     # node 1's copy was never delivered: counter stays 0
+        waited = time.perf_counter() - t0
+        assert 1.0 < waited < 30.0, waited
+        assert eng.get_option("wait_timeouts") == 1
+        assert not np.array_equal(eng.checksums(2, 9), o.checksum(o.fill_bytes(o.FILL_PATTERN, 9, size, SEED)))
+        # with the option off (the default) the flag is ignored and nothing waits
+        eng.set_option("wait_src", 0)
+        t0 = time.perf_counter()
+        eng.wait(eng.submit([d.Xfer(1, 2, 9, 4, 0, size, size)]))
+        assert time.perf_counter() - t0 < 1.0

@@ -141,3 +141,22 @@ def test_flag_relay_ok_recognises_device_ordered_relay_plans():
     frag = d.plan_relay([d.Xfer(0, dst, 5, 0, d.CHUNK_BYTES, size - d.CHUNK_BYTES, size) for dst in (1, 2)], 2)
     assert not any(x.flags & multi.XFER_WAIT_SRC for x in frag) and not multi.flag_relay_ok(frag)
     assert multi.flag_relay_ok(base)                                            # no rounds at all: nothing to order
+
+
+def test_store_sharing_and_multicast_group_helpers():
+    """multi.remote_touches / mcast_groups / fanout_plan: which buffers another rank's kernel touches (push: the destination's,
+    pull: the source's), which transfers form NVLS groups (same bytes, one source, >= 2 destinations on GPUs of their own),
+    and the BASELINE config-4 placement (239 deliveries on 8 nodes, seed never in its own destination set)."""
+    owner = lambda n: n
+    xs = [d.Xfer(0, 1, 5, 0, 0, 100, 100), d.Xfer(0, 2, 5, d.XFER_PULL, 0, 100, 100), d.Xfer(3, 3, 6, 0, 0, 10, 10)]
+    assert multi.remote_touches(xs, owner) == [(0, 5, 100, 2), (1, 5, 100, 0)]
+    assert multi.remote_touches(xs, lambda n: 0) == []                       # one GPU: nothing crosses
+    assert multi.mcast_groups(xs, owner) == [(5, 0, [1, 2])]
+    assert multi.mcast_groups(xs, lambda n: n % 2) == []                     # source and a destination share a GPU
+    holders, plan = multi.fanout_plan(d.Xfer, 8, 80, 1000, False)
+    assert len(plan) == 239 and all(holders[x.layer] == x.src_node != x.dst_node for x in plan)
+    assert sorted({len([x for x in plan if x.layer == l]) for l in range(80)}) == [2, 3, 4]
+    seed_holders, seed_plan = multi.fanout_plan(d.Xfer, 8, 80, 1000, True)
+    assert set(seed_holders.values()) == {0} and len(seed_plan) == 209
+    groups = multi.mcast_groups(plan, owner)
+    assert len(groups) == 80 and all(len(g[2]) >= 2 for g in groups)
