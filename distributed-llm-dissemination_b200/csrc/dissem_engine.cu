@@ -136,6 +136,9 @@ struct Sched {
     // some checksum entry that this schedule zeroes (an owned, partially covered chunk) is added into by kernels of
     // several GPUs: a relaunch must not zero it while another GPU's previous launch is still running
     bool cross_dev_shared = false;
+    // "wait_src" is on and the schedule carries relay hops that wait for their source on the device: rounds are then NOT
+    // separated by cross-GPU events (each GPU's stream runs its rounds in order; a hop waits only for its own upstream piece)
+    bool flag_ordered = false;
 };
 
 struct TicketPart {
@@ -453,6 +456,7 @@ static int compile_sched(dissem_ctx *ctx, const dissem_xfer *xfers, int n, Sched
             if ((x.flags & DISSEM_XFER_WAIT_SRC) && !src->host && ctx->opt_wait_src) {
                 d.wait_ptr = src->received();
                 d.wait_value = (unsigned long long)(x.off + x.size);
+                out->flag_ordered = true;
             }
             if (it.mc) {
                 uint8_t *mbase = reinterpret_cast<uint8_t *>(it.mc->va);
@@ -614,7 +618,8 @@ static int launch_sched(dissem_ctx *ctx, const Sched &s, Ticket *t) {
             const SchedPart &p = s.parts[k];
             DeviceState &ds = ctx->devs[p.dev_slot];
             CUDA_TRY(cudaSetDevice(ds.dev));
-            for (cudaEvent_t ev : prev_round) CUDA_TRY(cudaStreamWaitEvent(ds.stream, ev, 0));
+            if (!s.flag_ordered)
+                for (cudaEvent_t ev : prev_round) CUDA_TRY(cudaStreamWaitEvent(ds.stream, ev, 0));
             // buffers of other GPUs this part touches: wait until their owners' streams have finished writing them
             // (trailer zeroing at alloc / reset, fill, upload) -- streams of different GPUs are not ordered otherwise
             for (auto &nl : p.touch) {

@@ -319,9 +319,11 @@ int dissem_checksum_noalloc(int device, const void *data, int64_t size, uint64_t
  *  when every buffer involved is VMM-backed and local.  1 (default) = do so when a cost model built on the measured
  *  port rates says the plan gets shorter (i.e. it is bound by a source's egress); 3 = always; 0 = never (unicast
  *  fan-out); 2 = always, and single-destination transfers to another GPU too (a testing aid)),
- * "wait_src" (0 (default) = DISSEM_XFER_WAIT_SRC flags are ignored: inside one process round events already order relay
- *  hops, and a relaunch without dissem_layer_reset would find the counters already past their thresholds; 1 = honour
- *  them: the mode for one process per GPU, see DISSEM_XFER_WAIT_SRC), read-only "wait_timeouts",
+ * "wait_src" (0 (default) = DISSEM_XFER_WAIT_SRC flags are ignored: inside one process round events order relay hops, and
+ *  a relaunch without dissem_layer_reset would find the counters already past their thresholds; 1 = honour them: the
+ *  mode for one process per GPU, see DISSEM_XFER_WAIT_SRC.  A schedule compiled with flagged hops while the option is on
+ *  is ordered by those waits ALONE, also between the GPUs of one process: no cross-GPU event separates its rounds, so
+ *  the preconditions of DISSEM_XFER_WAIT_SRC are the caller's there too), read-only "wait_timeouts",
  * "mcast_variant" (kernel for schedule parts that carry multicast units: 0 (default) = register path whatever "variant"
  *  says, 1 = follow "variant"; transfers whose offset or size is not a multiple of 16 bytes are never multicast),
  * read-only: "mcast_supported" (do all local GPUs support multicast objects), "mcast_groups" (multicast

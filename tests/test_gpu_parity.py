@@ -945,9 +945,10 @@ def test_a_blocked_table_read_does_not_hold_up_other_senders():
 
 @pytest.mark.parametrize("variant", [0, 1])
 def test_relay_with_device_side_waits_in_one_process(variant):
-    """DISSEM_XFER_WAIT_SRC with "wait_src" on, inside ONE process: round events already order the hops, so every wait finds
-    its counter past the threshold — the kernels' wait path runs (both variants), nothing times out, and the store equals
-    the oracle's.  (Across processes the same flags carry the ordering; bench.py's parity leg checks that on >= 2 GPUs.)"""
+    """DISSEM_XFER_WAIT_SRC with "wait_src" on, inside ONE process: the schedule's rounds are then ordered by the device-side
+    waits alone (no cross-GPU events).  On one GPU the hops follow each other in the stream and every wait is satisfied at
+    once; on several GPUs the forwarding kernels really wait for their upstream pieces.  Both kernel variants; nothing
+    times out; the store equals the oracle's.  (Across processes: bench.py's parity leg on >= 2 GPUs.)"""
     size = 11 * d.CHUNK_BYTES + 4321
     n = max(1, min(_n_gpus(), 4))
     want = o.fill_bytes(o.FILL_PATTERN, 3, size, SEED)
@@ -975,6 +976,7 @@ def test_a_relay_wait_is_bounded():
     size = d.CHUNK_BYTES                              # one work unit: one bounded wait
     with d.Engine([0, 0, 0]) as eng:
         eng.set_option("wait_src", 1)
+        eng.set_option("unit_bytes", d.CHUNK_BYTES)   # (small transfers are otherwise cut into smaller units, each with its own wait)
         for node in (1, 2):
             eng.alloc(node, 9, size)
             eng.fill(node, 9, d.FILL_POISON)

@@ -49,12 +49,14 @@ def t_star(xfers, n, multicast):
     return max(max(e, i) for e, i in zip(eg, ing)) / (LINK_GBPS * 1e9), eg, ing
 
 
-def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, variant=1, relay=0, optimize=False):
+def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, variant=1, relay=0, optimize=False, flags=False):
     eng = d.Engine(list(range(n)))
     try:
         eng.set_option("variant", variant)
         eng.set_option("alloc_vmm", 1 if vmm else 0)
         eng.set_option("mcast", mcast)
+        if flags:
+            eng.set_option("wait_src", 1)        # rounds ordered by device-side waits alone: counters must start at zero
         for l, seed in holders.items():
             eng.alloc(seed, l, size)
             eng.fill(seed, l, d.FILL_PATTERN, 0x5EED)
@@ -69,9 +71,19 @@ def run_case(name, n, holders, xfers, size, vmm, mcast, directions, reps, varian
             name += f" -> {'relay, %d pieces' % relay if relay else 'unicast'}"
         s = eng.compile(xs)
         groups = eng.get_option("mcast_groups")
+        dsts = sorted({(x.dst_node, x.layer) for x in xfers})
+
+        def once():
+            if flags:
+                for (node, layer) in dsts:
+                    eng.reset(node, layer)
+            return eng.wait_detail(eng.launch(s))[0]
+
         for _ in range(2):
-            eng.wait(eng.launch(s))
-        times = [eng.wait_detail(eng.launch(s))[0] for _ in range(reps)]
+            once()
+        times = [once() for _ in range(reps)]
+        if flags:
+            assert eng.get_option("wait_timeouts") == 0
         ok = True
         for x in xfers[:: max(1, len(xfers) // 24)]:       # sample of destinations
             ref = eng.verify(x.src_node, x.layer)
@@ -119,8 +131,10 @@ def main():
     for c in cases:
         if c.startswith("relay"):            # relay16, relay32p (p = with direction choice)
             pieces = int("".join(ch for ch in c if ch.isdigit()) or 16)
-            run_case(f"{tag}/relay chains, {pieces} pieces" + (" + direction choice" if c.endswith("p") else ""), n, holders,
-                     xfers, args.size, vmm=False, mcast=0, directions=c.endswith("p"), reps=args.reps, relay=pieces)
+            fl = c.endswith("pf")                 # relay8pf: direction choice + hops ordered by device-side waits (no round events)
+            run_case(f"{tag}/relay chains, {pieces} pieces" + (" + direction choice" if c.endswith("p") or fl else "") +
+                     (", hops ordered on the device" if fl else ""), n, holders,
+                     xfers, args.size, vmm=False, mcast=0, directions=c.endswith("p") or fl, reps=args.reps, relay=pieces, flags=fl)
     if "optimized" in cases:
         run_case(f"{tag}/dissem_plan_optimize", n, holders, xfers, args.size, vmm=False, mcast=0, directions=False,
                  reps=args.reps, optimize=True)
