@@ -970,14 +970,14 @@ def run_ours(args, rank, world, local_rank):
                 "executed_plan": {"egress_bytes": eg, "ingress_bytes": ing, "local_bytes": loc, "busiest_port_bytes": busiest,
                                   "busiest_port_GBps": busiest / dev_step_s / 1e9},
                 "note": "achieved = best-sender busiest-port bytes / device time of a step (max over ranks)"}
-    cfg = bench_config(w, world, D)
-    cfg.update({"kernel_variant": "tma" if args.variant == 1 else "register", "transfers": len(xfers),
-                "transfers_pulled": sum(1 for x in xfers if x.flags & d.XFER_PULL), "relay_pieces": pieces,
-                "rounds": len(run.scheds), "units_per_step": run.units})
+    cfg = bench_config(w, world, D)                  # identical in the reference arm, key for key
+    plan_info = {"kernel_variant": "tma" if args.variant == 1 else "register", "transfers": len(xfers),
+                 "transfers_pulled": sum(1 for x in xfers if x.flags & d.XFER_PULL), "relay_pieces": pieces,
+                 "rounds": len(run.scheds), "units_per_step": run.units, "launches_per_step": run.launches}
     LINE.update({
         "metric": METRIC, "value": D / step_s / 1e9, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg, "plan": plan_info,
         "device_ms_per_step": dev_step_s * 1e3,
         "completion_time_ms": completion_ms, "completion_device_ms": completion_dev_ms,
         "completion_what": "median of %d single-shot disseminations: barrier, launch, wait, barrier (host clock, max over ranks); "

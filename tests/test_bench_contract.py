@@ -48,6 +48,8 @@ def test_our_arm_line():
     assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1
     c = j["clocks"]
     assert not ({"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} & set(c["reasons"]))
+    ref = _run("--impl", "reference", "--steps", "1", "--warmup", "0")
+    assert ref["config"] == j["config"]                     # the two arms describe the same workload, key for key
 
 
 def test_go_probe_reports_why():
