@@ -56,7 +56,7 @@ __device__ __forceinline__ void st_stream32(void *p, const U8 &v) {
 }
 // NVLS: one store lands in every GPU bound to the multicast object.
 __device__ __forceinline__ void st_multicast(uint4 *p, const uint4 &v) {
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p),
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p),
                  "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
                  "f"(__uint_as_float(v.w))
                  : "memory");
