@@ -66,3 +66,23 @@ def test_go_probe_reports_why():
         assert os.path.exists(p["binary"])
     j = _run("--impl", "reference", "--steps", "1", "--warmup", "0")
     assert "Go probe:" in j["note"]
+
+
+def test_best_sender_t_star_matches_the_hand_computed_port_loads():
+    """bench.py's roofline denominator at N >= 2: the busiest NVLink port under the BEST sender choice for config 2 with node i
+    on GPU i % N: 268 MB at 8 GPUs, 537 MB at 4, 805 MB at 2 (nodes served inside their own GPU cost no port),
+    divided by the measured 770 GB/s."""
+    sys.path.insert(0, ROOT)
+    import importlib
+    bench = importlib.import_module("bench")
+    import dissem_b200 as d
+    text = bench.config_text(bench.CFG2["size"], bench.CFG2["ring"])
+    plan = d.plan(text, bench.PLAN_MODE, time_scale=bench.TIME_SCALE)
+    stage = 4 * bench.CFG2["size"]
+    for world, want in ((8, stage), (4, 2 * stage), (2, 3 * stage)):
+        gpus = [n % world for n in range(bench.N_NODES)]
+        t_star, port = bench.best_sender_t_star(plan["nodes"], plan["assignment"], gpus, bench.CFG2["size"], world)
+        assert port == want, (world, port)
+        assert abs(t_star - want / 770e9) < 1e-12
+    # one GPU: everything is local, nothing crosses a port
+    assert bench.best_sender_t_star(plan["nodes"], plan["assignment"], [0] * 8, bench.CFG2["size"], 1) == (0.0, 0)
